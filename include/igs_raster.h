@@ -1,0 +1,177 @@
+/* libigs_raster -- B200 (sm_100a) differentiable tile-based Gaussian-splatting
+ * rasterizer.  C ABI: plain pointers and sizes, no torch types, no C++
+ * exceptions across the boundary.
+ *
+ * This is the drop-in boundary for the reference's native rasterizer
+ * ("DGR" = /root/reference/submodules/diff-gaussian-rasterization):
+ *
+ *   igs_forward       replaces CudaRasterizer::Rasterizer::forward
+ *                     (DGR cuda_rasterizer/rasterizer.h:35-61, called from
+ *                     RasterizeGaussiansCUDA, DGR rasterize_points.cu:35-133,
+ *                     pybind name rasterize_gaussians, DGR ext.cpp:16)
+ *   igs_backward      replaces CudaRasterizer::Rasterizer::backward
+ *                     (rasterizer.h:63-100; RasterizeGaussiansBackwardCUDA,
+ *                     rasterize_points.cu:135-239; ext.cpp:17)
+ *   igs_mark_visible  replaces CudaRasterizer::Rasterizer::markVisible
+ *                     (rasterizer.h:24-29; rasterize_points.cu:241-260;
+ *                     ext.cpp:18)
+ *   igs_*_bytes / igs_*_layout replace the reference's std::function<char*(size_t)>
+ *                     resize callbacks and GeometryState/BinningState/ImageState
+ *                     ::fromChunk (DGR rasterizer_impl.h:22-72): the caller
+ *                     asks for sizes up front and owns every buffer.
+ *
+ * Ownership: the caller owns all memory; the library allocates no device
+ * memory.  Buffers marked [keep] must stay alive and unmodified until the
+ * matching igs_backward; [scratch] may be reused by the next call on the same
+ * stream.  All device pointers must be 16-byte aligned (torch allocations are).
+ * All launches go to the given stream.  Re-entrant per (device, stream) as long
+ * as each stream uses its own scratch/ctrl buffers.
+ *
+ * Errors: every entry point returns IGS_OK (0) or a negative IGS_ERR_* code;
+ * igs_last_error() returns a thread-local message.  With args->debug != 0 the
+ * stream is synchronised and checked after every stage (the reference's
+ * CHECK_CUDA, DGR cuda_rasterizer/auxiliary.h:167-174).
+ */
+#ifndef IGS_RASTER_H
+#define IGS_RASTER_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IGS_OK 0
+#define IGS_ERR_INVALID (-1)   /* bad argument */
+#define IGS_ERR_CUDA (-2)      /* CUDA runtime error, see igs_last_error() */
+#define IGS_ERR_CAPACITY (-3)  /* num_rendered > capacity: grow [bin]/[sort] and call igs_forward_bin_render */
+
+#define IGS_MAX_EXTRA_DIMS 34  /* DGR cuda_rasterizer/auxiliary.h:20 */
+#define IGS_TILE 16            /* DGR cuda_rasterizer/config.h:16-17 */
+
+typedef void* igs_stream_t; /* cudaStream_t */
+
+typedef struct IgsFwdArgs {
+  /* sizes: P gaussians, D active SH degree, M SH coefficients stored per
+   * gaussian (may exceed (D+1)^2), ED extra-attribute channels */
+  int32_t P, D, M, ED;
+  int32_t W, H;
+  float tan_fovx, tan_fovy, scale_modifier;
+  int32_t prefiltered, debug;
+  /* camera (device) */
+  const float* bg;          /* [3] */
+  const float* viewmatrix;  /* [16] row-vector convention (transposed W2C) */
+  const float* projmatrix;  /* [16] */
+  const float* campos;      /* [3] */
+  /* gaussians (device, contiguous fp32; NULL = not provided) */
+  const float* means3D;         /* [P,3] */
+  const float* shs;             /* [P,M,3] or NULL */
+  const float* colors_precomp;  /* [P,3] or NULL */
+  const float* opacities;       /* [P] */
+  const float* scales;          /* [P,3] */
+  const float* rotations;       /* [P,4] */
+  const float* cov3Ds_precomp;  /* [P,6] or NULL */
+  const float* norm3Ds_precomp; /* [P,3] or NULL */
+  const float* extra_attrs;     /* [P,ED] or NULL */
+  /* outputs (device); every element is written, no pre-zeroing needed */
+  float* out_color; /* [3,H,W] */
+  float* out_depth; /* [1,H,W] */
+  float* out_norm;  /* [3,H,W] un-normalised */
+  float* out_alpha; /* [1,H,W] */
+  float* out_extra; /* [ED,H,W] or NULL */
+  int32_t* radii;   /* [P] */
+  /* workspaces (device) */
+  void* geom;   /* [keep]    igs_geom_bytes(P) */
+  void* img;    /* [keep]    igs_img_bytes(W,H) */
+  void* bin;    /* [keep]    igs_bin_bytes(capacity) */
+  void* sort;   /* [scratch] igs_sort_bytes(capacity) */
+  void* ctrl;   /* [scratch] igs_ctrl_bytes(P,capacity): scan/sort look-back state */
+  int64_t capacity; /* instance capacity of bin/sort */
+  /* pinned host slot the library copies num_rendered into */
+  int32_t* num_rendered_pinned;
+} IgsFwdArgs;
+
+typedef struct IgsBwdArgs {
+  int32_t P, D, M, ED;
+  int32_t W, H;
+  float tan_fovx, tan_fovy, scale_modifier;
+  int32_t debug;
+  int64_t num_rendered;
+  const float* bg;
+  const float* viewmatrix;
+  const float* projmatrix;
+  const float* campos;
+  const float* means3D;
+  const float* shs;
+  const float* colors_precomp;
+  const float* scales;
+  const float* rotations;
+  const float* cov3Ds_precomp;
+  const float* norm3Ds_precomp;
+  const float* extra_attrs;
+  const int32_t* radii;
+  /* forward state */
+  const void* geom;
+  const void* img;
+  const void* bin;
+  const float* out_alpha; /* [1,H,W] as returned by forward */
+  /* upstream gradients (device, contiguous) */
+  const float* dL_dcolor; /* [3,H,W] */
+  const float* dL_ddepth; /* [1,H,W] */
+  const float* dL_dnorm;  /* [3,H,W] */
+  const float* dL_dalpha; /* [1,H,W] */
+  const float* dL_dextra; /* [ED,H,W] or NULL */
+  /* [scratch] igs_accum_bytes(P,ED); zeroed by the library */
+  void* accum;
+  /* outputs (device); every element is written, no pre-zeroing needed */
+  float* dL_dmeans2D;   /* [P,3] (.z = 0) */
+  float* dL_dcolors;    /* [P,3] */
+  float* dL_dopacity;   /* [P,1] */
+  float* dL_dmeans3D;   /* [P,3] */
+  float* dL_dcov3D;     /* [P,6] */
+  float* dL_dnorm3D;    /* [P,3] */
+  float* dL_dsh;        /* [P,M,3] or NULL */
+  float* dL_dscales;    /* [P,3] */
+  float* dL_drotations; /* [P,4] */
+  float* dL_dextra_attrs; /* [P,ED] or NULL */
+} IgsBwdArgs;
+
+const char* igs_version(void);
+const char* igs_last_error(void);
+
+size_t igs_geom_bytes(int32_t P);
+size_t igs_img_bytes(int32_t W, int32_t H);
+size_t igs_bin_bytes(int64_t capacity);
+size_t igs_sort_bytes(int64_t capacity);
+size_t igs_ctrl_bytes(int32_t P, int64_t capacity);
+size_t igs_accum_bytes(int32_t P, int32_t ED);
+
+/* Byte offsets of the arrays inside the workspaces (for tests / inspection).
+ * geom  (7): splat records float4[P][4], tiles_touched u32[P],
+ *            point_offsets u32[P], norm3D float[P][3], rgb float[P][3],
+ *            clamped u8[P], depths float[P]
+ * bin   (2): point_list u32[cap], keys u64[cap]      (sorted)
+ * img   (2): ranges uint2[T], n_contrib u32[H*W] */
+void igs_geom_layout(int32_t P, int64_t* off7);
+void igs_bin_layout(int64_t capacity, int64_t* off2);
+void igs_img_layout(int32_t W, int32_t H, int64_t* off2);
+
+/* Full forward.  Launches preprocess+scan, copies num_rendered to the pinned
+ * slot, speculatively launches binning/sort/render for `capacity` instances,
+ * then waits for the copy only.  *num_rendered receives the instance count.
+ * Returns IGS_ERR_CAPACITY if it exceeds capacity: outputs are then invalid and
+ * the caller re-runs the second half with bigger bin/sort/ctrl buffers. */
+int igs_forward(const IgsFwdArgs* args, igs_stream_t stream, int64_t* num_rendered);
+
+/* Second half only (duplicate, sort, ranges, render), after IGS_ERR_CAPACITY. */
+int igs_forward_bin_render(const IgsFwdArgs* args, igs_stream_t stream);
+
+int igs_backward(const IgsBwdArgs* args, igs_stream_t stream);
+
+int igs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
+                     const float* projmatrix, uint8_t* present, igs_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -147,12 +147,12 @@ size_t igs_ctrl_bytes(int32_t P, int64_t capacity);
 size_t igs_accum_bytes(int32_t P, int32_t ED);
 
 /* Byte offsets of the arrays inside the workspaces (for tests / inspection).
- * geom  (7): splat records float4[P][4], tiles_touched u32[P],
- *            point_offsets u32[P], norm3D float[P][3], rgb float[P][3],
- *            clamped u8[P], depths float[P]
+ * geom  (4): splat records float4[P][4] = {conic.xyz,opacity | x,y,depth,extra0 |
+ *            r,g,b,nx | ny,nz,-,-}, tiles_touched u32[P], point_offsets u32[P]
+ *            (inclusive scan), clamped u8[P] (bit c = colour channel c clamped)
  * bin   (2): point_list u32[cap], keys u64[cap]      (sorted)
  * img   (2): ranges uint2[T], n_contrib u32[H*W] */
-void igs_geom_layout(int32_t P, int64_t* off7);
+void igs_geom_layout(int32_t P, int64_t* off4);
 void igs_bin_layout(int64_t capacity, int64_t* off2);
 void igs_img_layout(int32_t W, int32_t H, int64_t* off2);
 

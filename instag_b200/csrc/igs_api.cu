@@ -1,0 +1,290 @@
+// C ABI of libigs_raster (include/igs_raster.h): argument validation, workspace
+// carving, stage orchestration, error reporting.  No device memory is
+// allocated here; the only host<->device traffic is the 4-byte num_rendered
+// copy, which the host waits for AFTER it has queued every forward kernel.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include "igs_common.cuh"
+#include "igs_kernels.cuh"
+
+namespace igs {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+}
+
+int check_cuda(cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return IGS_OK;
+  set_error("%s: %s", what, cudaGetErrorString(e));
+  return IGS_ERR_CUDA;
+}
+
+// reference CHECK_CUDA (auxiliary.h:167-174): with debug, sync + check per stage
+int stage_check(bool debug, cudaStream_t s, const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess && debug) e = cudaStreamSynchronize(s);
+  return check_cuda(e, what);
+}
+
+static int num_passes(int grid_x, int grid_y) {
+  const int bits = 32 + higher_msb((uint32_t)(grid_x * grid_y)); // reference rasterizer_impl.cu:303-311
+  return (bits + RADIX_BITS - 1) / RADIX_BITS;
+}
+
+struct EventCache { // one reusable event per host thread
+  cudaEvent_t ev = nullptr;
+  cudaEvent_t get() {
+    if (!ev) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    return ev;
+  }
+};
+static thread_local EventCache g_event;
+
+static int validate_fwd(const IgsFwdArgs* a) {
+  if (!a) { set_error("null args"); return IGS_ERR_INVALID; }
+  if (a->P < 0 || a->W <= 0 || a->H <= 0) { set_error("bad sizes P=%d W=%d H=%d", a->P, a->W, a->H); return IGS_ERR_INVALID; }
+  if (a->ED < 0 || a->ED > IGS_MAX_EXTRA_DIMS) { set_error("ED=%d out of range [0,%d]", a->ED, IGS_MAX_EXTRA_DIMS); return IGS_ERR_INVALID; }
+  if ((a->shs == nullptr) == (a->colors_precomp == nullptr) && a->P > 0) {
+    set_error("provide exactly one of shs / colors_precomp"); return IGS_ERR_INVALID;
+  }
+  if (a->shs && (a->D < 0 || a->D > 3 || a->M < (a->D + 1) * (a->D + 1))) {
+    set_error("sh degree %d needs M >= %d, got %d", a->D, (a->D + 1) * (a->D + 1), a->M); return IGS_ERR_INVALID;
+  }
+  if (a->P > 0 && (!a->means3D || !a->opacities || !a->scales || !a->rotations)) {
+    set_error("means3D, opacities, scales, rotations are required"); return IGS_ERR_INVALID;
+  }
+  if (a->ED > 0 && !a->extra_attrs && a->P > 0) { set_error("ED>0 but extra_attrs is null"); return IGS_ERR_INVALID; }
+  if (!a->out_color || !a->out_depth || !a->out_norm || !a->out_alpha || (a->ED > 0 && !a->out_extra)) {
+    set_error("null output"); return IGS_ERR_INVALID;
+  }
+  if (!a->geom || !a->img || !a->bin || !a->sort || !a->ctrl || a->capacity < 0 || !a->num_rendered_pinned) {
+    set_error("null workspace"); return IGS_ERR_INVALID;
+  }
+  if (a->capacity >= (1ll << 30)) { set_error("capacity must be < 2^30 instances"); return IGS_ERR_INVALID; }
+  return IGS_OK;
+}
+
+static PreArgs make_pre(const IgsFwdArgs* a) {
+  PreArgs p{};
+  const GeomLayout gl(a->P);
+  const CtrlLayout cl(a->P, a->capacity);
+  char* g = (char*)a->geom;
+  char* c = (char*)a->ctrl;
+  p.P = a->P; p.D = a->D; p.M = a->M; p.ED = a->ED; p.W = a->W; p.H = a->H;
+  p.grid_x = (a->W + TILE - 1) / TILE; p.grid_y = (a->H + TILE - 1) / TILE;
+  p.prefiltered = a->prefiltered;
+  p.tan_fovx = a->tan_fovx; p.tan_fovy = a->tan_fovy;
+  p.focal_y = a->H / (2.0f * a->tan_fovy); // reference rasterizer_impl.cu:228-229
+  p.focal_x = a->W / (2.0f * a->tan_fovx);
+  p.scale_modifier = a->scale_modifier;
+  p.capacity = a->capacity;
+  p.viewmatrix = a->viewmatrix; p.projmatrix = a->projmatrix; p.campos = a->campos;
+  p.means3D = a->means3D; p.shs = a->shs; p.colors_precomp = a->colors_precomp; p.opacities = a->opacities;
+  p.scales = a->scales; p.rotations = a->rotations; p.cov3Ds_precomp = a->cov3Ds_precomp;
+  p.norm3Ds_precomp = a->norm3Ds_precomp; p.extra_attrs = a->extra_attrs;
+  p.radii = a->radii;
+  p.splat = (float4*)(g + gl.splat);
+  p.tiles_touched = (uint32_t*)(g + gl.tiles_touched);
+  p.point_offsets = (uint32_t*)(g + gl.point_offsets);
+  p.clamped = (uint8_t*)(g + gl.clamped);
+  p.scan_state = (unsigned long long*)(c + cl.scan_state);
+  p.header = (CtrlHeader*)(c + cl.header);
+  return p;
+}
+
+static int run_bin_render(const IgsFwdArgs* a, cudaStream_t s) {
+  const GeomLayout gl(a->P);
+  const ImgLayout il(a->W, a->H);
+  const BinLayout bl(a->capacity);
+  const SortLayout sl(a->capacity);
+  const CtrlLayout cl(a->P, a->capacity);
+  char* g = (char*)a->geom; char* im = (char*)a->img; char* b = (char*)a->bin;
+  char* so = (char*)a->sort; char* c = (char*)a->ctrl;
+  const bool debug = a->debug != 0;
+
+  BinArgs ba{};
+  ba.P = a->P;
+  ba.grid_x = (a->W + TILE - 1) / TILE; ba.grid_y = (a->H + TILE - 1) / TILE;
+  ba.passes = num_passes(ba.grid_x, ba.grid_y);
+  ba.capacity = a->capacity;
+  ba.radii = a->radii;
+  ba.splat = (const float4*)(g + gl.splat);
+  ba.point_offsets = (const uint32_t*)(g + gl.point_offsets);
+  ba.header = (CtrlHeader*)(c + cl.header);
+  ba.hist = (uint32_t*)(c + cl.hist);
+  ba.lookback = (uint32_t*)(c + cl.lookback);
+  ba.sort_blocks = cl.sort_blocks;
+  // the LAST pass must land in the [keep] bin workspace: buffer index passes&1
+  const int keep = ba.passes & 1;
+  ba.keys[keep] = (uint64_t*)(b + bl.keys);       ba.vals[keep] = (uint32_t*)(b + bl.point_list);
+  ba.keys[keep ^ 1] = (uint64_t*)(so + sl.keys_alt); ba.vals[keep ^ 1] = (uint32_t*)(so + sl.vals_alt);
+  ba.ranges = (uint2*)(im + il.ranges);
+  ba.num_tiles = ba.grid_x * ba.grid_y;
+  launch_binning(ba, s);
+  if (int r = stage_check(debug, s, "binning (duplicate/sort/ranges)")) return r;
+
+  RenderArgs ra{};
+  ra.W = a->W; ra.H = a->H; ra.ED = a->ED; ra.grid_x = ba.grid_x; ra.grid_y = ba.grid_y;
+  ra.ranges = ba.ranges;
+  ra.point_list = (const uint32_t*)(b + bl.point_list);
+  ra.splat = ba.splat;
+  ra.extra_attrs = a->extra_attrs;
+  ra.bg = a->bg;
+  ra.out_color = a->out_color; ra.out_depth = a->out_depth; ra.out_norm = a->out_norm;
+  ra.out_alpha = a->out_alpha; ra.out_extra = a->out_extra;
+  ra.n_contrib = (uint32_t*)(im + il.n_contrib);
+  launch_render(ra, s);
+  return stage_check(debug, s, "render");
+}
+
+// zero the look-back / histogram / ticket state; keeps header.num_rendered when asked
+static int reset_ctrl(const IgsFwdArgs* a, cudaStream_t s, bool keep_header) {
+  const CtrlLayout cl(a->P, a->capacity);
+  char* c = (char*)a->ctrl;
+  if (keep_header) {
+    CtrlHeader* h = (CtrlHeader*)(c + cl.header);
+    if (int r = check_cuda(cudaMemsetAsync(h->ticket, 0, sizeof(h->ticket), s), "memset ticket")) return r;
+    return check_cuda(cudaMemsetAsync(c + cl.hist, 0, cl.total - cl.hist, s), "memset ctrl");
+  }
+  return check_cuda(cudaMemsetAsync(c, 0, cl.total, s), "memset ctrl");
+}
+
+} // namespace igs
+
+using namespace igs;
+
+extern "C" {
+
+const char* igs_version(void) { return "libigs_raster 0.1 (sm_100a)"; }
+const char* igs_last_error(void) { return g_err; }
+
+size_t igs_geom_bytes(int32_t P) { return GeomLayout(P).total; }
+size_t igs_img_bytes(int32_t W, int32_t H) { return ImgLayout(W, H).total; }
+size_t igs_bin_bytes(int64_t capacity) { return BinLayout(capacity).total; }
+size_t igs_sort_bytes(int64_t capacity) { return SortLayout(capacity).total; }
+size_t igs_ctrl_bytes(int32_t P, int64_t capacity) { return CtrlLayout(P, capacity).total; }
+size_t igs_accum_bytes(int32_t P, int32_t ED) { return accum_bytes(P, ED); }
+
+void igs_geom_layout(int32_t P, int64_t* off) {
+  const GeomLayout l(P);
+  off[0] = (int64_t)l.splat; off[1] = (int64_t)l.tiles_touched; off[2] = (int64_t)l.point_offsets; off[3] = (int64_t)l.clamped;
+}
+void igs_bin_layout(int64_t capacity, int64_t* off) {
+  const BinLayout l(capacity);
+  off[0] = (int64_t)l.point_list; off[1] = (int64_t)l.keys;
+}
+void igs_img_layout(int32_t W, int32_t H, int64_t* off) {
+  const ImgLayout l(W, H);
+  off[0] = (int64_t)l.ranges; off[1] = (int64_t)l.n_contrib;
+}
+
+int igs_forward(const IgsFwdArgs* a, igs_stream_t stream, int64_t* num_rendered) {
+  if (int r = validate_fwd(a)) return r;
+  cudaStream_t s = (cudaStream_t)stream;
+  const bool debug = a->debug != 0;
+  if (num_rendered) *num_rendered = 0;
+  if (int r = reset_ctrl(a, s, false)) return r;
+  if (a->P == 0) { // reference rasterize_points.cu:93: outputs stay at their fill value
+    const size_t HW = (size_t)a->W * a->H;
+    cudaMemsetAsync(a->out_depth, 0, HW * 4, s); cudaMemsetAsync(a->out_alpha, 0, HW * 4, s);
+    cudaMemsetAsync(a->out_norm, 0, 3 * HW * 4, s); cudaMemsetAsync(a->out_color, 0, 3 * HW * 4, s);
+    if (a->ED > 0) cudaMemsetAsync(a->out_extra, 0, (size_t)a->ED * HW * 4, s);
+    *a->num_rendered_pinned = 0;
+    return stage_check(debug, s, "empty forward");
+  }
+  const PreArgs pa = make_pre(a);
+  launch_preprocess(pa, s);
+  if (int r = stage_check(debug, s, "preprocess")) return r;
+  if (int r = check_cuda(cudaMemcpyAsync(a->num_rendered_pinned, &pa.header->num_rendered, sizeof(int32_t),
+                                         cudaMemcpyDeviceToHost, s), "copy num_rendered")) return r;
+  cudaEvent_t ev = g_event.get();
+  if (int r = check_cuda(cudaEventRecord(ev, s), "event record")) return r;
+  // speculative second half: sized by capacity, bounded on the device by num_rendered
+  if (int r = run_bin_render(a, s)) return r;
+  if (int r = check_cuda(cudaEventSynchronize(ev), "wait num_rendered")) return r;
+  const int64_t n = (int64_t)(uint32_t)*a->num_rendered_pinned;
+  if (num_rendered) *num_rendered = n;
+  if (n > a->capacity) {
+    set_error("num_rendered %lld exceeds capacity %lld", (long long)n, (long long)a->capacity);
+    return IGS_ERR_CAPACITY;
+  }
+  return IGS_OK;
+}
+
+int igs_forward_bin_render(const IgsFwdArgs* a, igs_stream_t stream) {
+  if (int r = validate_fwd(a)) return r;
+  cudaStream_t s = (cudaStream_t)stream;
+  // new ctrl buffer: bring num_rendered over from the pinned slot
+  const CtrlLayout cl(a->P, a->capacity);
+  if (int r = check_cuda(cudaMemsetAsync(a->ctrl, 0, cl.total, s), "memset ctrl")) return r;
+  CtrlHeader* h = (CtrlHeader*)((char*)a->ctrl + cl.header);
+  if (int r = check_cuda(cudaMemcpyAsync(&h->num_rendered, a->num_rendered_pinned, sizeof(int32_t),
+                                         cudaMemcpyHostToDevice, s), "restore num_rendered")) return r;
+  return run_bin_render(a, s);
+}
+
+int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
+  if (!a) { set_error("null args"); return IGS_ERR_INVALID; }
+  if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->ED < 0 || a->ED > IGS_MAX_EXTRA_DIMS) { set_error("bad sizes"); return IGS_ERR_INVALID; }
+  if (a->P == 0) return IGS_OK; // reference rasterize_points.cu:194
+  if (!a->accum || !a->geom || !a->img || !a->bin || !a->out_alpha || !a->dL_dcolor || !a->dL_ddepth ||
+      !a->dL_dnorm || !a->dL_dalpha || (a->ED > 0 && !a->dL_dextra)) { set_error("null buffer"); return IGS_ERR_INVALID; }
+  cudaStream_t s = (cudaStream_t)stream;
+  const bool debug = a->debug != 0;
+  const GeomLayout gl(a->P);
+  const ImgLayout il(a->W, a->H);
+  const BinLayout bl(a->num_rendered);
+  const char* g = (const char*)a->geom; const char* im = (const char*)a->img; const char* b = (const char*)a->bin;
+  if (int r = check_cuda(cudaMemsetAsync(a->accum, 0, accum_bytes(a->P, a->ED), s), "memset accum")) return r;
+
+  BwdRenderArgs ra{};
+  ra.W = a->W; ra.H = a->H; ra.ED = a->ED;
+  ra.grid_x = (a->W + TILE - 1) / TILE; ra.grid_y = (a->H + TILE - 1) / TILE;
+  ra.ranges = (const uint2*)(im + il.ranges);
+  ra.point_list = (const uint32_t*)(b + 0); // point_list is the first array of the bin workspace for any capacity
+  (void)bl;
+  ra.splat = (const float4*)(g + gl.splat);
+  ra.extra_attrs = a->extra_attrs; ra.bg = a->bg; ra.out_alpha = a->out_alpha;
+  ra.n_contrib = (const uint32_t*)(im + il.n_contrib);
+  ra.dL_dcolor = a->dL_dcolor; ra.dL_ddepth = a->dL_ddepth; ra.dL_dnorm = a->dL_dnorm;
+  ra.dL_dalpha = a->dL_dalpha; ra.dL_dextra = a->dL_dextra;
+  ra.accum = (float*)a->accum;
+  ra.accum_extra = a->ED > 1 ? (float*)((char*)a->accum + align_up((size_t)a->P * ACC_F * sizeof(float))) : nullptr;
+  if (a->num_rendered > 0) launch_render_backward(ra, s);
+  if (int r = stage_check(debug, s, "render backward")) return r;
+
+  BwdPreArgs pa{};
+  pa.P = a->P; pa.D = a->D; pa.M = a->M; pa.ED = a->ED; pa.W = a->W; pa.H = a->H;
+  pa.tan_fovx = a->tan_fovx; pa.tan_fovy = a->tan_fovy;
+  pa.focal_y = a->H / (2.0f * a->tan_fovy); pa.focal_x = a->W / (2.0f * a->tan_fovx);
+  pa.scale_modifier = a->scale_modifier;
+  pa.viewmatrix = a->viewmatrix; pa.projmatrix = a->projmatrix; pa.campos = a->campos;
+  pa.means3D = a->means3D; pa.shs = a->shs; pa.scales = a->scales; pa.rotations = a->rotations;
+  pa.cov3Ds_precomp = a->cov3Ds_precomp; pa.norm3Ds_precomp = a->norm3Ds_precomp;
+  pa.radii = a->radii;
+  pa.splat = ra.splat;
+  pa.clamped = (const uint8_t*)(g + gl.clamped);
+  pa.accum = ra.accum; pa.accum_extra = ra.accum_extra;
+  pa.dL_dmeans2D = a->dL_dmeans2D; pa.dL_dcolors = a->dL_dcolors; pa.dL_dopacity = a->dL_dopacity;
+  pa.dL_dmeans3D = a->dL_dmeans3D; pa.dL_dcov3D = a->dL_dcov3D; pa.dL_dnorm3D = a->dL_dnorm3D;
+  pa.dL_dsh = a->dL_dsh; pa.dL_dscales = a->dL_dscales; pa.dL_drotations = a->dL_drotations;
+  pa.dL_dextra_attrs = a->dL_dextra_attrs;
+  launch_preprocess_backward(pa, s);
+  return stage_check(debug, s, "preprocess backward");
+}
+
+int igs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, igs_stream_t stream) {
+  (void)projmatrix; // the reference's test only uses the view-space depth (auxiliary.h:155)
+  if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) { set_error("bad arguments"); return IGS_ERR_INVALID; }
+  launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
+  return stage_check(false, (cudaStream_t)stream, "mark_visible");
+}
+
+} // extern "C"

@@ -1,0 +1,163 @@
+// libigs_raster internal header: workspace layouts, error plumbing, fp32
+// helpers.  sm_100a only.
+#pragma once
+#include <cstdint>
+#include <cstddef>
+#include <cstdio>
+#include <cuda_runtime.h>
+#include "../../include/igs_raster.h"
+
+namespace igs {
+
+constexpr int TILE = IGS_TILE;        // 16x16 pixel tiles (reference config.h:16-17)
+constexpr int TILE_PIX = TILE * TILE; // 256 threads per render CTA, one per pixel
+constexpr float NEAR_Z = 0.2f;        // reference auxiliary.h:155
+constexpr float ALPHA_MIN = 1.0f / 255.0f;
+constexpr float T_MIN = 0.0001f;
+
+// ---- per-Gaussian splat record: 4 x float4 = 64 B, one aligned gather ------
+//  r0 = {conic.x, conic.y, conic.z, opacity}
+//  r1 = {mean2D.x, mean2D.y, view depth, extra[0]}
+//  r2 = {r, g, b, normal.x}
+//  r3 = {normal.y, normal.z, -, -}
+constexpr int SPLAT_F4 = 4;
+
+// ---- gradient accumulator: 16 floats = 64 B per Gaussian -------------------
+//  0,1 dL/dmean2D.xy | 2,3,4 dL/dconic.{x,y,w} | 5 dL/dopacity | 6..8 dL/dcolor
+//  9 dL/ddepth | 10..12 dL/dnormal | 13 dL/dextra[0] | 14,15 unused
+constexpr int ACC_F = 16;
+
+__host__ __device__ inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
+
+struct GeomLayout {
+  size_t splat, tiles_touched, point_offsets, clamped, total;
+  __host__ __device__ explicit GeomLayout(int P) {
+    size_t o = 0, p = (size_t)(P > 0 ? P : 1);
+    splat = o;          o = align_up(o + p * SPLAT_F4 * sizeof(float4));
+    tiles_touched = o;  o = align_up(o + p * sizeof(uint32_t));
+    point_offsets = o;  o = align_up(o + p * sizeof(uint32_t));
+    clamped = o;        o = align_up(o + p * sizeof(uint8_t));
+    total = o;
+  }
+};
+
+struct ImgLayout {
+  size_t ranges, n_contrib, total;
+  __host__ __device__ ImgLayout(int W, int H) {
+    size_t T = (size_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
+    size_t o = 0;
+    ranges = o;     o = align_up(o + (T ? T : 1) * sizeof(uint2));
+    n_contrib = o;  o = align_up(o + (size_t)(W * H > 0 ? W * H : 1) * sizeof(uint32_t));
+    total = o;
+  }
+};
+
+struct BinLayout { // sorted result, kept for backward
+  size_t point_list, keys, total;
+  __host__ __device__ explicit BinLayout(int64_t cap) {
+    size_t c = (size_t)(cap > 0 ? cap : 1), o = 0;
+    point_list = o;  o = align_up(o + c * sizeof(uint32_t));
+    keys = o;        o = align_up(o + c * sizeof(uint64_t));
+    total = o;
+  }
+};
+
+struct SortLayout { // ping-pong partner of BinLayout, scratch
+  size_t vals_alt, keys_alt, total;
+  __host__ __device__ explicit SortLayout(int64_t cap) {
+    size_t c = (size_t)(cap > 0 ? cap : 1), o = 0;
+    vals_alt = o;  o = align_up(o + c * sizeof(uint32_t));
+    keys_alt = o;  o = align_up(o + c * sizeof(uint64_t));
+    total = o;
+  }
+};
+
+// radix sort geometry
+constexpr int RADIX_BITS = 8;
+constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 8;                          // keys per thread
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;   // keys per CTA per pass
+constexpr int MAX_PASSES = 8;
+constexpr int PRE_THREADS = 256;
+
+struct CtrlHeader {
+  uint32_t num_rendered;       // written by the preprocess kernel's last CTA
+  uint32_t overflow;           // num_rendered > capacity
+  uint32_t ticket[MAX_PASSES]; // dynamic CTA ids of the onesweep passes
+  uint32_t pad[6];
+};
+
+struct CtrlLayout {
+  size_t header, scan_state, hist, lookback, total;
+  int sort_blocks;
+  __host__ __device__ CtrlLayout(int P, int64_t cap) {
+    size_t o = 0;
+    int pre_blocks = (P + PRE_THREADS - 1) / PRE_THREADS;
+    sort_blocks = (int)((cap + SORT_TILE - 1) / SORT_TILE);
+    if (sort_blocks < 1) sort_blocks = 1;
+    header = o;      o = align_up(o + sizeof(CtrlHeader));
+    scan_state = o;  o = align_up(o + (size_t)(pre_blocks ? pre_blocks : 1) * sizeof(unsigned long long));
+    hist = o;        o = align_up(o + (size_t)MAX_PASSES * RADIX * sizeof(uint32_t));
+    lookback = o;    o = align_up(o + (size_t)MAX_PASSES * sort_blocks * RADIX * sizeof(uint32_t));
+    total = o;
+  }
+};
+
+inline size_t accum_bytes(int P, int ED) {
+  size_t p = (size_t)(P > 0 ? P : 1);
+  size_t extra = ED > 1 ? (size_t)(ED - 1) : 0; // channels 1.. live in a side array
+  return align_up(p * ACC_F * sizeof(float)) + align_up(p * extra * sizeof(float));
+}
+
+// reference rasterizer_impl.cu:35-50 getHigherMsb: number of tile-id bits sorted
+inline int higher_msb(uint32_t n) {
+  uint32_t msb = sizeof(n) * 4, step = msb;
+  while (step > 1) {
+    step /= 2;
+    if (n >> msb) msb += step; else msb -= step;
+  }
+  if (n >> msb) msb++;
+  return (int)msb;
+}
+
+// error plumbing (igs_api.cu)
+void set_error(const char* fmt, ...);
+int check_cuda(cudaError_t e, const char* what);
+int stage_check(bool debug, cudaStream_t s, const char* what);
+
+// ---- device helpers ---------------------------------------------------------
+// a0*b0 + a1*b1 + a2*b2 with the contraction nvcc applies to that expression
+// (left product of the first sum fused, see DESIGN.md "FMA contraction");
+// spelled with intrinsics so the result does not depend on compiler mood.
+__device__ __forceinline__ float dot3c(float a0, float b0, float a1, float b1, float a2, float b2) {
+  return __fmaf_rn(a2, b2, __fmaf_rn(a0, b0, __fmul_rn(a1, b1)));
+}
+
+// m[r]*x + m[4+r]*y + m[8+r]*z + m[12+r]   (reference auxiliary.h:59-78)
+__device__ __forceinline__ float xform_row(const float* __restrict__ m, int r, float x, float y, float z) {
+  return __fadd_rn(dot3c(m[r], x, m[4 + r], y, m[8 + r], z), m[12 + r]);
+}
+
+// reference auxiliary.h:42-45: evaluated in double, contracted to one DFMA
+__device__ __forceinline__ float ndc2pix(float v, int S) {
+  return (float)(__fma_rn((double)v + 1.0, (double)S, -1.0) * 0.5);
+}
+
+// reference auxiliary.h:47-57 (max_radius is an int there)
+__device__ __forceinline__ void tile_rect(float px, float py, int radius, int gx, int gy,
+                                          int& x0, int& y0, int& x1, int& y1) {
+  const float r = (float)radius;
+  x0 = min(gx, max(0, (int)(__fsub_rn(px, r) * 0.0625f)));
+  y0 = min(gy, max(0, (int)(__fsub_rn(py, r) * 0.0625f)));
+  x1 = min(gx, max(0, (int)(__fsub_rn(__fadd_rn(__fadd_rn(px, r), 16.f), 1.f) * 0.0625f)));
+  y1 = min(gy, max(0, (int)(__fsub_rn(__fadd_rn(__fadd_rn(py, r), 16.f), 1.f) * 0.0625f)));
+}
+
+// -0.5(a dx^2 + c dy^2) - b dx dy, contraction as in reference forward.cu:406
+__device__ __forceinline__ float gauss_power(float cx, float cy, float cz, float dx, float dy) {
+  const float s = __fmaf_rn(__fmul_rn(cx, dx), dx, __fmul_rn(__fmul_rn(cz, dy), dy));
+  return __fmaf_rn(s, -0.5f, -__fmul_rn(__fmul_rn(cy, dx), dy));
+}
+
+} // namespace igs

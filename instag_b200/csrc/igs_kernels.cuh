@@ -1,0 +1,88 @@
+// Kernel argument blocks and host-side launchers of libigs_raster.
+#pragma once
+#include "igs_common.cuh"
+
+namespace igs {
+
+struct PreArgs {
+  int P, D, M, ED, W, H, grid_x, grid_y, prefiltered;
+  float tan_fovx, tan_fovy, focal_x, focal_y, scale_modifier;
+  int64_t capacity;
+  const float *viewmatrix, *projmatrix, *campos;
+  const float *means3D, *shs, *colors_precomp, *opacities, *scales, *rotations;
+  const float *cov3Ds_precomp, *norm3Ds_precomp, *extra_attrs;
+  int32_t* radii;
+  float4* splat;
+  uint32_t* tiles_touched;
+  uint32_t* point_offsets;
+  uint8_t* clamped;
+  unsigned long long* scan_state;
+  CtrlHeader* header;
+};
+
+struct BinArgs {
+  int P, grid_x, grid_y;
+  int passes;          // 8-bit digit passes covering 32 + tile bits
+  int64_t capacity;
+  const int32_t* radii;
+  const float4* splat;
+  const uint32_t* point_offsets;
+  CtrlHeader* header;
+  uint32_t* hist;      // [MAX_PASSES][256]
+  uint32_t* lookback;  // [passes][sort_blocks][256]
+  int sort_blocks;
+  // ping-pong buffers; buf 0 receives the duplicated keys, the last pass
+  // writes into (keys_out, vals_out) = the [keep] bin workspace
+  uint64_t* keys[2];
+  uint32_t* vals[2];
+  uint2* ranges;       // [T]
+  int num_tiles;
+};
+
+struct RenderArgs {
+  int W, H, ED, grid_x, grid_y;
+  const uint2* ranges;
+  const uint32_t* point_list;
+  const float4* splat;
+  const float* extra_attrs; // [P,ED], used for channels >= 1
+  const float* bg;
+  float *out_color, *out_depth, *out_norm, *out_alpha, *out_extra;
+  uint32_t* n_contrib;
+};
+
+struct BwdRenderArgs {
+  int W, H, ED, grid_x, grid_y;
+  const uint2* ranges;
+  const uint32_t* point_list;
+  const float4* splat;
+  const float* extra_attrs;
+  const float* bg;
+  const float* out_alpha;
+  const uint32_t* n_contrib;
+  const float *dL_dcolor, *dL_ddepth, *dL_dnorm, *dL_dalpha, *dL_dextra;
+  float* accum;       // [P][16]
+  float* accum_extra; // [P][ED-1] or NULL
+};
+
+struct BwdPreArgs {
+  int P, D, M, ED, W, H;
+  float tan_fovx, tan_fovy, focal_x, focal_y, scale_modifier;
+  const float *viewmatrix, *projmatrix, *campos;
+  const float *means3D, *shs, *scales, *rotations, *cov3Ds_precomp, *norm3Ds_precomp;
+  const int32_t* radii;
+  const float4* splat;
+  const uint8_t* clamped;
+  const float* accum;
+  const float* accum_extra;
+  float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dnorm3D, *dL_dsh;
+  float *dL_dscales, *dL_drotations, *dL_dextra_attrs;
+};
+
+void launch_preprocess(const PreArgs& a, cudaStream_t s);
+void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s);
+void launch_binning(const BinArgs& a, cudaStream_t s);     // duplicate + sort + ranges
+void launch_render(const RenderArgs& a, cudaStream_t s);
+void launch_render_backward(const BwdRenderArgs& a, cudaStream_t s);
+void launch_preprocess_backward(const BwdPreArgs& a, cudaStream_t s);
+
+} // namespace igs

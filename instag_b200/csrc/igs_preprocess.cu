@@ -1,0 +1,253 @@
+// Stage 1 of the forward path: per-Gaussian preprocess (EWA projection, 3D->2D
+// covariance, SH->RGB, radius, tile rectangle) fused with the inclusive prefix
+// sum of tiles_touched (single-pass decoupled look-back), so that one launch
+// replaces the reference's preprocessCUDA + cub::DeviceScan::InclusiveSum
+// (reference forward.cu:203-316, rasterizer_impl.cu:280).  Also markVisible.
+//
+// Bound: HBM.  Algorithmic bytes per Gaussian: reads 44 (+12*(D+1)^2 SH),
+// writes 64 (splat record) + 4 radii + 4 tiles + 4 offsets (+1 clamp mask).
+#include "igs_common.cuh"
+#include "igs_kernels.cuh"
+#include "igs_math.cuh"
+
+namespace igs {
+
+__device__ __constant__ float kSH_C0 = 0.28209479177387814f;
+__device__ __constant__ float kSH_C1 = 0.4886025119029199f;
+__device__ __constant__ float kSH_C2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
+                                           -1.0925484305920792f, 0.5462742152960396f};
+__device__ __constant__ float kSH_C3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f,
+                                           0.3731763325901154f, -0.4570457994644658f, 1.445305721320277f,
+                                           -0.5900435899266435f};
+
+// SH -> RGB (reference forward.cu:20-71); returns colour, sets clamp mask bits
+__device__ __forceinline__ float3 sh_to_rgb(int deg, const float* __restrict__ sh, float x, float y, float z,
+                                            uint32_t& clamp_mask) {
+  float res[3];
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+#define SHK(k) __ldg(sh + 3 * (k) + c)
+    float r = __fmul_rn(kSH_C0, SHK(0));
+    if (deg > 0) {
+      r = __fmaf_rn(kSH_C0, SHK(0), -__fmul_rn(__fmul_rn(kSH_C1, y), SHK(1)));
+      r = __fmaf_rn(__fmul_rn(kSH_C1, z), SHK(2), r);
+      r = __fmaf_rn(-__fmul_rn(kSH_C1, x), SHK(3), r);
+      if (deg > 1) {
+        const float xx = __fmul_rn(x, x), yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+        const float xy = __fmul_rn(x, y), yz = __fmul_rn(y, z), xz = __fmul_rn(x, z);
+        r = __fmaf_rn(__fmul_rn(kSH_C2[0], xy), SHK(4), r);
+        r = __fmaf_rn(__fmul_rn(kSH_C2[1], yz), SHK(5), r);
+        r = __fmaf_rn(__fmul_rn(kSH_C2[2], __fmaf_rn(-y, y, __fmaf_rn(2.f, zz, -xx))), SHK(6), r);
+        r = __fmaf_rn(__fmul_rn(kSH_C2[3], xz), SHK(7), r);
+        r = __fmaf_rn(__fmul_rn(kSH_C2[4], __fmaf_rn(x, x, -yy)), SHK(8), r);
+        if (deg > 2) {
+          r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[0], y), __fmaf_rn(3.f, xx, -yy)), SHK(9), r);
+          r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[1], xy), z), SHK(10), r);
+          r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[2], y), __fmaf_rn(-y, y, __fmaf_rn(4.f, zz, -xx))), SHK(11), r);
+          r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[3], z),
+                                  __fmaf_rn(-3.f, yy, __fmaf_rn(2.f, zz, -__fmul_rn(3.f, xx)))), SHK(12), r);
+          r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[4], x), __fmaf_rn(-y, y, __fmaf_rn(4.f, zz, -xx))), SHK(13), r);
+          r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[5], z), __fmaf_rn(x, x, -yy)), SHK(14), r);
+          r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[6], x), __fmaf_rn(x, x, -__fmul_rn(3.f, yy))), SHK(15), r);
+        }
+      }
+    }
+#undef SHK
+    r = __fadd_rn(r, 0.5f);
+    if (r < 0.f) clamp_mask |= 1u << c;
+    res[c] = fmaxf(r, 0.f);
+  }
+  return make_float3(res[0], res[1], res[2]);
+}
+
+// ---- single-pass inclusive scan state (decoupled look-back) ----------------
+// 64-bit word per CTA: high 32 bits = flag (0 empty, 1 aggregate, 2 inclusive
+// prefix), low 32 bits = value.  One 64-bit store/load keeps them consistent.
+constexpr unsigned long long FLAG_AGG = 1ull << 32, FLAG_PREFIX = 2ull << 32;
+
+__device__ __forceinline__ unsigned long long ld_state(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_state(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// Exclusive prefix of this CTA's total over all previous CTAs; executed by
+// warp 0.  Windows of 32 predecessors are inspected at once.
+__device__ __forceinline__ uint32_t lookback_exclusive(unsigned long long* state, int bid, uint32_t total) {
+  const int lane = threadIdx.x & 31;
+  if (bid == 0) {
+    if (lane == 0) st_state(state, FLAG_PREFIX | total);
+    return 0;
+  }
+  if (lane == 0) st_state(state + bid, FLAG_AGG | total);
+  uint32_t excl = 0;
+  int base = bid - 1;
+  while (true) {
+    const int j = base - lane;
+    unsigned long long v = j >= 0 ? ld_state(state + j) : FLAG_PREFIX; // virtual prefix 0 before CTA 0
+    const uint32_t flag = (uint32_t)(v >> 32);
+    const unsigned ready = __ballot_sync(0xffffffffu, flag != 0);
+    const unsigned pref = __ballot_sync(0xffffffffu, flag == 2);
+    // lanes 0..first-1 must all be ready, where first = nearest lane holding a prefix
+    const int first = pref ? __ffs(pref) - 1 : 32;
+    const unsigned need = first >= 31 ? 0xffffffffu : ((2u << first) - 1);
+    if ((ready & need) != need) continue; // somebody in the window has not published yet
+    uint32_t val = (lane <= first) ? (uint32_t)v : 0u;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+    excl += val;
+    if (pref) break;
+    base -= 32;
+  }
+  if (lane == 0) st_state(state + bid, FLAG_PREFIX | (unsigned long long)(uint32_t)(excl + total));
+  return excl;
+}
+
+template <bool USE_SH>
+__global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
+  __shared__ float s_view[16], s_proj[16], s_cam[3];
+  __shared__ uint32_t s_warp_sum[PRE_THREADS / 32];
+  __shared__ uint32_t s_excl;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid < 16) { s_view[tid] = __ldg(a.viewmatrix + tid); s_proj[tid] = __ldg(a.projmatrix + tid); }
+  if (tid < 3) s_cam[tid] = __ldg(a.campos + tid);
+  __syncthreads();
+
+  const int idx = blockIdx.x * PRE_THREADS + tid;
+  uint32_t tiles = 0;
+  int radius = 0;
+  if (idx < a.P) {
+    const float px = __ldg(a.means3D + 3 * idx), py = __ldg(a.means3D + 3 * idx + 1), pz = __ldg(a.means3D + 3 * idx + 2);
+    const float vz = xform_row(s_view, 2, px, py, pz);
+    if (vz <= NEAR_Z) { // reference auxiliary.h:155 (NaN passes, as there)
+      if (a.prefiltered) { printf("Point is filtered although prefiltered is set. This shouldn't happen!"); __trap(); }
+    } else {
+      const float hx = xform_row(s_proj, 0, px, py, pz), hy = xform_row(s_proj, 1, px, py, pz);
+      const float hw = xform_row(s_proj, 3, px, py, pz);
+      const float p_w = __fdiv_rn(1.0f, __fadd_rn(hw, 0.0000001f));
+      const float ndc_x = __fmul_rn(hx, p_w), ndc_y = __fmul_rn(hy, p_w);
+
+      const float3 sc = make_float3(__ldg(a.scales + 3 * idx), __ldg(a.scales + 3 * idx + 1), __ldg(a.scales + 3 * idx + 2));
+      const float4 q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
+      const Rot R = quat_to_rot(q);
+      float c3[6];
+      if (a.cov3Ds_precomp) {
+#pragma unroll
+        for (int k = 0; k < 6; k++) c3[k] = __ldg(a.cov3Ds_precomp + 6 * idx + k);
+      } else {
+        cov3d_from_scale_rot(sc, a.scale_modifier, R, c3);
+      }
+      const float tx = xform_row(s_view, 0, px, py, pz), ty = xform_row(s_view, 1, px, py, pz);
+      const float3 cov = cov2d(tx, ty, vz, a.focal_x, a.focal_y, a.tan_fovx, a.tan_fovy, c3, s_view);
+      const float det = __fmaf_rn(cov.x, cov.z, -__fmul_rn(cov.y, cov.y));
+      if (det != 0.0f) {
+        const float det_inv = __fdiv_rn(1.f, det);
+        const float mid = __fmul_rn(0.5f, __fadd_rn(cov.x, cov.z));
+        const float disc = __fsqrt_rn(fmaxf(0.1f, __fmaf_rn(mid, mid, -det)));
+        const float lam = fmaxf(__fadd_rn(mid, disc), __fsub_rn(mid, disc));
+        const float my_radius = ceilf(__fmul_rn(3.f, __fsqrt_rn(lam)));
+        const float sx = ndc2pix(ndc_x, a.W), sy = ndc2pix(ndc_y, a.H);
+        int x0, y0, x1, y1;
+        tile_rect(sx, sy, (int)my_radius, a.grid_x, a.grid_y, x0, y0, x1, y1);
+        const uint32_t n_tiles = (uint32_t)((x1 - x0) * (y1 - y0));
+        if (n_tiles != 0) {
+          tiles = n_tiles;
+          radius = (int)my_radius;
+          // normal: rotated axis of the smallest RAW scale, flipped to face the camera
+          float nx, ny, nz;
+          if (a.norm3Ds_precomp) {
+            nx = __ldg(a.norm3Ds_precomp + 3 * idx); ny = __ldg(a.norm3Ds_precomp + 3 * idx + 1);
+            nz = __ldg(a.norm3Ds_precomp + 3 * idx + 2);
+          } else {
+            int k = 0;
+            if (sc.x > sc.z && sc.y > sc.z) k = 2;
+            else if (sc.x > sc.y && sc.z > sc.y) k = 1;
+            nx = R.m[0][k]; ny = R.m[1][k]; nz = R.m[2][k];
+            const float rx = __fsub_rn(px, s_cam[0]), ry = __fsub_rn(py, s_cam[1]), rz = __fsub_rn(pz, s_cam[2]);
+            if (dot3c(rx, nx, ry, ny, rz, nz) > 0.f) { nx = -nx; ny = -ny; nz = -nz; }
+          }
+          float3 rgb;
+          if (USE_SH) {
+            float dx = __fsub_rn(px, s_cam[0]), dy = __fsub_rn(py, s_cam[1]), dz = __fsub_rn(pz, s_cam[2]);
+            const float len = __fsqrt_rn(dot3c(dx, dx, dy, dy, dz, dz));
+            dx = __fdiv_rn(dx, len); dy = __fdiv_rn(dy, len); dz = __fdiv_rn(dz, len);
+            uint32_t mask = 0;
+            rgb = sh_to_rgb(a.D, a.shs + (size_t)idx * a.M * 3, dx, dy, dz, mask);
+            a.clamped[idx] = (uint8_t)mask;
+          } else {
+            rgb = make_float3(__ldg(a.colors_precomp + 3 * idx), __ldg(a.colors_precomp + 3 * idx + 1),
+                              __ldg(a.colors_precomp + 3 * idx + 2));
+          }
+          const float e0 = a.extra_attrs ? __ldg(a.extra_attrs + (size_t)idx * a.ED) : 0.f;
+          float4* rec = a.splat + (size_t)idx * SPLAT_F4;
+          rec[0] = make_float4(__fmul_rn(cov.z, det_inv), __fmul_rn(-cov.y, det_inv), __fmul_rn(cov.x, det_inv),
+                               __ldg(a.opacities + idx));
+          rec[1] = make_float4(sx, sy, vz, e0);
+          rec[2] = make_float4(rgb.x, rgb.y, rgb.z, nx);
+          rec[3] = make_float4(ny, nz, 0.f, 0.f);
+        }
+      }
+    }
+    a.radii[idx] = radius;
+    a.tiles_touched[idx] = tiles;
+  }
+
+  // block inclusive scan of `tiles`
+  uint32_t incl = tiles;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t n = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += n;
+  }
+  if (lane == 31) s_warp_sum[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t w = lane < PRE_THREADS / 32 ? s_warp_sum[lane] : 0u;
+    uint32_t wi = w;
+#pragma unroll
+    for (int o = 1; o < PRE_THREADS / 32; o <<= 1) {
+      const uint32_t n = __shfl_up_sync(0xffffffffu, wi, o);
+      if (lane >= o) wi += n;
+    }
+    const uint32_t total = __shfl_sync(0xffffffffu, wi, PRE_THREADS / 32 - 1);
+    if (lane < PRE_THREADS / 32) s_warp_sum[lane] = wi - w; // exclusive warp offsets
+    const uint32_t excl = lookback_exclusive(a.scan_state, blockIdx.x, total);
+    if (lane == 0) {
+      s_excl = excl;
+      if (blockIdx.x == gridDim.x - 1) {
+        a.header->num_rendered = excl + total;
+        a.header->overflow = (int64_t)(excl + total) > a.capacity ? 1u : 0u;
+      }
+    }
+  }
+  __syncthreads();
+  if (idx < a.P) a.point_offsets[idx] = s_excl + s_warp_sum[warp] + incl;
+}
+
+__global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
+                                    uint8_t* __restrict__ present) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  float m[16];
+#pragma unroll
+  for (int k = 0; k < 16; k++) m[k] = __ldg(view + k);
+  const float vz = xform_row(m, 2, __ldg(means3D + 3 * idx), __ldg(means3D + 3 * idx + 1), __ldg(means3D + 3 * idx + 2));
+  present[idx] = !(vz <= NEAR_Z);
+}
+
+void launch_preprocess(const PreArgs& a, cudaStream_t s) {
+  if (a.P <= 0) return;
+  const int blocks = (a.P + PRE_THREADS - 1) / PRE_THREADS;
+  if (a.shs) preprocess_kernel<true><<<blocks, PRE_THREADS, 0, s>>>(a);
+  else preprocess_kernel<false><<<blocks, PRE_THREADS, 0, s>>>(a);
+}
+
+void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s) {
+  if (P <= 0) return;
+  mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, view, present);
+}
+
+} // namespace igs

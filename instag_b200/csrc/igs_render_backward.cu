@@ -1,0 +1,199 @@
+// Backward of the compositing stage (reference renderCUDA, backward.cu:473-712).
+//
+// One CTA per tile, one thread per pixel, back-to-front traversal, T recovered
+// by division exactly as the reference does (backward.cu:612).  Where the
+// reference issues 13+ED global float atomics per accepted pixel-Gaussian pair,
+// this kernel first reduces the 14 partial gradients over the 32 pixels of a
+// warp with a TRANSPOSING butterfly (16 shuffles for 16 values instead of
+// 16*5), after which lane 2k holds the warp total of value k and the warp
+// issues one coalesced 14-lane red.global.add into the Gaussian's 64-byte
+// accumulator row.  Gaussians no lane of the warp touches are skipped with one
+// ballot; the tail of the list behind every pixel's last contributor is skipped
+// without being loaded.
+//
+// Bound: FP32 issue + L2 atomics.  Per blended pair ~110 flop.
+#include "igs_common.cuh"
+#include "igs_kernels.cuh"
+
+namespace igs {
+
+constexpr int BATCH = TILE_PIX;
+
+__device__ __forceinline__ void thread_pixel_b(int tid, int& lx, int& ly) {
+  const int w = tid >> 5, l = tid & 31;
+  lx = (w & 1) * 8 + (l & 7);
+  ly = (w >> 1) * 4 + (l >> 3);
+}
+
+// Sum 16 per-lane values over the warp; lane l returns the total of v[l>>1].
+__device__ __forceinline__ float warp_transpose_reduce16(const float (&v)[16], int lane) {
+  constexpr unsigned FULL = 0xffffffffu;
+  float w8[8], w4[4], w2[2];
+  const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    const float send = b4 ? v[i] : v[i + 8], keep = b4 ? v[i + 8] : v[i];
+    w8[i] = keep + __shfl_xor_sync(FULL, send, 16);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const float send = b3 ? w8[i] : w8[i + 4], keep = b3 ? w8[i + 4] : w8[i];
+    w4[i] = keep + __shfl_xor_sync(FULL, send, 8);
+  }
+#pragma unroll
+  for (int i = 0; i < 2; i++) {
+    const float send = b2 ? w4[i] : w4[i + 2], keep = b2 ? w4[i + 2] : w4[i];
+    w2[i] = keep + __shfl_xor_sync(FULL, send, 4);
+  }
+  const float send = b1 ? w2[0] : w2[1], keep = b1 ? w2[1] : w2[0];
+  const float w1 = keep + __shfl_xor_sync(FULL, send, 2);
+  return w1 + __shfl_xor_sync(FULL, w1, 1);
+}
+
+template <int ED_T> // 0, 1, or -1 = generic
+__global__ void __launch_bounds__(TILE_PIX) render_backward_kernel(BwdRenderArgs a) {
+  __shared__ float4 s_r0[BATCH];
+  __shared__ float4 s_r1[BATCH];
+  __shared__ float4 s_r2[BATCH];
+  __shared__ float2 s_r3[BATCH];
+  __shared__ uint32_t s_id[BATCH];
+  __shared__ uint32_t s_max_contrib;
+
+  const int tid = threadIdx.x, lane = tid & 31;
+  int lx, ly;
+  thread_pixel_b(tid, lx, ly);
+  const int px = blockIdx.x * TILE + lx, py = blockIdx.y * TILE + ly;
+  const bool inside = px < a.W && py < a.H;
+  const float pxf = (float)px, pyf = (float)py;
+  const size_t HW = (size_t)a.H * a.W, pix = (size_t)py * a.W + px;
+  const uint2 range = a.ranges[blockIdx.y * a.grid_x + blockIdx.x];
+  const int total = (int)(range.y - range.x);
+  const int ED = ED_T < 0 ? a.ED : ED_T;
+
+  const float T_final = inside ? __fsub_rn(1.f, a.out_alpha[pix]) : 0.f;
+  float T = T_final;
+  const int last_contributor = inside ? (int)a.n_contrib[pix] : 0;
+
+  float dpc0 = 0, dpc1 = 0, dpc2 = 0, dpd = 0, dpn0 = 0, dpn1 = 0, dpn2 = 0, dpa = 0, dpe0 = 0;
+  if (inside) {
+    dpc0 = a.dL_dcolor[pix]; dpc1 = a.dL_dcolor[HW + pix]; dpc2 = a.dL_dcolor[2 * HW + pix];
+    dpd = a.dL_ddepth[pix];
+    dpn0 = a.dL_dnorm[pix]; dpn1 = a.dL_dnorm[HW + pix]; dpn2 = a.dL_dnorm[2 * HW + pix];
+    dpa = a.dL_dalpha[pix];
+    if (ED >= 1) dpe0 = a.dL_dextra[pix];
+  }
+  float ac0 = 0, ac1 = 0, ac2 = 0, ad = 0, an0 = 0, an1 = 0, an2 = 0, aa = 0, ae0 = 0; // accum_re*
+  float lc0 = 0, lc1 = 0, lc2 = 0, ld = 0, ln0 = 0, ln1 = 0, ln2 = 0, le0 = 0, last_alpha = 0; // last_*
+  float ax[ED_T < 0 ? IGS_MAX_EXTRA_DIMS : 1], lxe[ED_T < 0 ? IGS_MAX_EXTRA_DIMS : 1];
+  if (ED_T < 0) {
+#pragma unroll
+    for (int c = 0; c < IGS_MAX_EXTRA_DIMS; c++) { ax[c] = 0.f; lxe[c] = 0.f; }
+  }
+  const float bg_dot = __ldg(a.bg) * dpc0 + __ldg(a.bg + 1) * dpc1 + __ldg(a.bg + 2) * dpc2;
+  const float ddelx_dx = 0.5f * a.W, ddely_dy = 0.5f * a.H;
+
+  // nothing behind the last contributor of ANY pixel of the tile matters
+  if (tid == 0) s_max_contrib = 0;
+  __syncthreads();
+  const int warp_max = (int)__reduce_max_sync(0xffffffffu, (unsigned)last_contributor);
+  if (lane == 0) atomicMax(&s_max_contrib, (unsigned)warp_max);
+  __syncthreads();
+  const int block_max = (int)s_max_contrib;
+
+  // r = reversed index (0 = last instance of the tile); forward position = total - r
+  for (int rbase = total - block_max; rbase < total; rbase += BATCH) {
+    __syncthreads();
+    const int n = min(BATCH, total - rbase);
+    if (tid < n) {
+      const uint32_t id = __ldg(a.point_list + range.y - 1 - (rbase + tid));
+      const float4* rec = a.splat + (size_t)id * SPLAT_F4;
+      s_id[tid] = id;
+      s_r0[tid] = __ldg(rec);
+      s_r1[tid] = __ldg(rec + 1);
+      s_r2[tid] = __ldg(rec + 2);
+      const float4 r3 = __ldg(rec + 3);
+      s_r3[tid] = make_float2(r3.x, r3.y);
+    }
+    __syncthreads();
+    // first j this warp cares about: contributor = total - (rbase+j) - 1 < warp_max
+    const int j0 = max(0, total - rbase - warp_max);
+    for (int j = j0; j < n; j++) {
+      const int contributor = total - (rbase + j) - 1;
+      const float4 r1 = s_r1[j];
+      const float4 r0 = s_r0[j];
+      const float dx = __fsub_rn(r1.x, pxf), dy = __fsub_rn(r1.y, pyf);
+      const float power = gauss_power(r0.x, r0.y, r0.z, dx, dy);
+      const float G = expf(power);
+      const float alpha = fminf(0.99f, __fmul_rn(r0.w, G));
+      const bool valid = contributor < last_contributor && !(power > 0.0f) && !(alpha < ALPHA_MIN);
+      if (!__any_sync(0xffffffffu, valid)) continue;
+      float v[16];
+#pragma unroll
+      for (int k = 0; k < 16; k++) v[k] = 0.f;
+      float weight = 0.f;
+      if (valid) {
+        const float4 r2 = s_r2[j];
+        const float2 r3 = s_r3[j];
+        T = __fdiv_rn(T, __fsub_rn(1.f, alpha));
+        weight = alpha * T;
+        const float om = 1.f - last_alpha;
+        float dL_dalpha = 0.f;
+        ac0 = last_alpha * lc0 + om * ac0; lc0 = r2.x; dL_dalpha += (r2.x - ac0) * dpc0; v[6] = weight * dpc0;
+        ac1 = last_alpha * lc1 + om * ac1; lc1 = r2.y; dL_dalpha += (r2.y - ac1) * dpc1; v[7] = weight * dpc1;
+        ac2 = last_alpha * lc2 + om * ac2; lc2 = r2.z; dL_dalpha += (r2.z - ac2) * dpc2; v[8] = weight * dpc2;
+        ad = last_alpha * ld + om * ad; ld = r1.z; dL_dalpha += (r1.z - ad) * dpd; v[9] = weight * dpd;
+        an0 = last_alpha * ln0 + om * an0; ln0 = r2.w; dL_dalpha += (r2.w - an0) * dpn0; v[10] = weight * dpn0;
+        an1 = last_alpha * ln1 + om * an1; ln1 = r3.x; dL_dalpha += (r3.x - an1) * dpn1; v[11] = weight * dpn1;
+        an2 = last_alpha * ln2 + om * an2; ln2 = r3.y; dL_dalpha += (r3.y - an2) * dpn2; v[12] = weight * dpn2;
+        if (ED >= 1) {
+          ae0 = last_alpha * le0 + om * ae0; le0 = r1.w; dL_dalpha += (r1.w - ae0) * dpe0; v[13] = weight * dpe0;
+        }
+        if (ED_T < 0) {
+          const float* e = a.extra_attrs + (size_t)s_id[j] * ED;
+          for (int c = 1; c < ED; c++) {
+            const float ev = __ldg(e + c);
+            ax[c] = last_alpha * lxe[c] + om * ax[c]; lxe[c] = ev;
+            dL_dalpha += (ev - ax[c]) * a.dL_dextra[c * HW + pix];
+          }
+        }
+        aa = last_alpha + om * aa;                    // reference backward.cu:674-675
+        dL_dalpha += (1.f - aa) * dpa;
+        dL_dalpha *= T;
+        last_alpha = alpha;
+        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot; // reference backward.cu:684-687
+        const float dL_dG = r0.w * dL_dalpha;
+        const float gdx = G * dx, gdy = G * dy;
+        const float dG_ddelx = -gdx * r0.x - gdy * r0.y;
+        const float dG_ddely = -gdy * r0.z - gdx * r0.y;
+        v[0] = dL_dG * dG_ddelx * ddelx_dx;
+        v[1] = dL_dG * dG_ddely * ddely_dy;
+        v[2] = -0.5f * gdx * dx * dL_dG;
+        v[3] = -0.5f * gdx * dy * dL_dG;
+        v[4] = -0.5f * gdy * dy * dL_dG;
+        v[5] = G * dL_dalpha;
+      }
+      const float tot = warp_transpose_reduce16(v, lane);
+      const uint32_t id = s_id[j];
+      const int k = lane >> 1;
+      if (!(lane & 1) && k < 13 + (ED >= 1 ? 1 : 0)) atomicAdd(a.accum + (size_t)id * ACC_F + k, tot);
+      if (ED_T < 0) { // channels 1.. : plain warp reduction into the side array
+        for (int c = 1; c < ED; c++) {
+          float gsum = valid ? weight * a.dL_dextra[c * HW + pix] : 0.f;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) gsum += __shfl_xor_sync(0xffffffffu, gsum, o);
+          if (lane == 0) atomicAdd(a.accum_extra + (size_t)id * (ED - 1) + (c - 1), gsum);
+        }
+      }
+    }
+  }
+}
+
+void launch_render_backward(const BwdRenderArgs& a, cudaStream_t s) {
+  if (a.W <= 0 || a.H <= 0) return;
+  const dim3 grid(a.grid_x, a.grid_y);
+  if (a.ED == 0) render_backward_kernel<0><<<grid, TILE_PIX, 0, s>>>(a);
+  else if (a.ED == 1) render_backward_kernel<1><<<grid, TILE_PIX, 0, s>>>(a);
+  else render_backward_kernel<-1><<<grid, TILE_PIX, 0, s>>>(a);
+}
+
+} // namespace igs

@@ -1,0 +1,325 @@
+"""Host side of the drop-in: the reference's Python API over libigs_raster.
+
+Mirrors submodules/diff-gaussian-rasterization/diff_gauss/__init__.py of the
+reference ("DGR"): same names, argument order, defaults, return tuple, error
+texts and debug-snapshot behaviour, so that gaussian_renderer/__init__.py:15
+(`from diff_gauss import GaussianRasterizationSettings, GaussianRasterizer`)
+runs unmodified.  PyTorch supplies device memory, streams and autograd; every
+kernel is in libigs_raster.so (no fallback path exists).
+"""
+import ctypes as C
+from typing import NamedTuple
+
+import torch
+import torch.nn as nn
+
+from . import _native as N
+
+
+def cpu_deep_copy_tuple(input_tuple):
+    # DGR diff_gauss/__init__.py:17-19
+    return tuple(item.cpu().clone() if isinstance(item, torch.Tensor) else item for item in input_tuple)
+
+
+class _DeviceScratch:
+    """Per-device reusable scratch: sort ping-pong partner, look-back state,
+    gradient accumulators, the pinned num_rendered slot, a capacity estimate."""
+
+    def __init__(self, device):
+        self.device = device
+        self.sort = None
+        self.ctrl = None
+        self.accum = None
+        self.pinned = torch.zeros(4, dtype=torch.int32).pin_memory()
+        self.capacity_hint = {}
+        self.zero_imgs = {}
+
+    def buf(self, name, nbytes):
+        t = getattr(self, name)
+        if t is None or t.numel() < nbytes:
+            t = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=self.device)
+            setattr(self, name, t)
+        return t
+
+    def zeros_like_img(self, C_, H, W):
+        key = (C_, H, W)
+        z = self.zero_imgs.get(key)
+        if z is None:
+            z = torch.zeros((C_, H, W), dtype=torch.float32, device=self.device)
+            self.zero_imgs[key] = z
+        return z
+
+
+_scratch = {}
+
+
+def _get_scratch(device):
+    s = _scratch.get(device)
+    if s is None:
+        s = _scratch[device] = _DeviceScratch(device)
+    return s
+
+
+def _ptr(t):
+    """Device pointer of a tensor, NULL for the reference's empty-tensor 'None' sentinels."""
+    return t.data_ptr() if (t is not None and t.numel() != 0) else None
+
+
+def _f32c(t):
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t if t.is_contiguous() else t.contiguous()
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    # DGR diff_gauss/__init__.py:180-192
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+
+
+def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier,
+                    cov3Ds_precomp, norm3Ds_precomp, extra_attrs, ED, viewmatrix, projmatrix, tanfovx,
+                    tanfovy, image_height, image_width, sh, sh_degree, campos, prefiltered, debug):
+    """Equivalent of _C.rasterize_gaussians (DGR rasterize_points.cu:35-133)."""
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    if not means3D.is_cuda:
+        raise RuntimeError("libigs_raster is CUDA-only: means3D must be a CUDA tensor (no CPU fallback)")
+    lib = N.lib()
+    dev = means3D.device
+    P, H, W = means3D.size(0), int(image_height), int(image_width)
+    M = sh.size(1) if sh.numel() != 0 else 0
+    f32 = dict(dtype=torch.float32, device=dev)
+    u8 = dict(dtype=torch.uint8, device=dev)
+    color = torch.empty((3, H, W), **f32)
+    depth = torch.empty((1, H, W), **f32)
+    norm = torch.empty((3, H, W), **f32)
+    alpha = torch.empty((1, H, W), **f32)
+    extra = torch.empty((ED, H, W), **f32) if ED > 0 else torch.empty((0,), **f32)
+    radii = torch.empty((P,), dtype=torch.int32, device=dev)
+
+    sc = _get_scratch(dev)
+    hint_key = (P, H, W)
+    capacity = sc.capacity_hint.get(hint_key)
+    if capacity is None:
+        capacity = max(8 * P, 1 << 16)
+    geom = torch.empty(lib.igs_geom_bytes(P), **u8)
+    img = torch.empty(lib.igs_img_bytes(W, H), **u8)
+    binb = torch.empty(lib.igs_bin_bytes(capacity), **u8)
+    sort = sc.buf("sort", lib.igs_sort_bytes(capacity))
+    ctrl = sc.buf("ctrl", lib.igs_ctrl_bytes(P, capacity))
+
+    keep = [_f32c(bg), _f32c(viewmatrix), _f32c(projmatrix), _f32c(campos), _f32c(means3D), _f32c(sh),
+            _f32c(colors_precomp), _f32c(opacities), _f32c(scales), _f32c(rotations),
+            _f32c(cov3Ds_precomp), _f32c(norm3Ds_precomp), _f32c(extra_attrs)]
+    a = N.IgsFwdArgs()
+    a.P, a.D, a.M, a.ED, a.W, a.H = P, int(sh_degree), M, ED, W, H
+    a.tan_fovx, a.tan_fovy, a.scale_modifier = tanfovx, tanfovy, scale_modifier
+    a.prefiltered, a.debug = int(bool(prefiltered)), int(bool(debug))
+    (a.bg, a.viewmatrix, a.projmatrix, a.campos, a.means3D, a.shs, a.colors_precomp, a.opacities, a.scales,
+     a.rotations, a.cov3Ds_precomp, a.norm3Ds_precomp, a.extra_attrs) = [_ptr(t) for t in keep]
+    a.out_color, a.out_depth, a.out_norm, a.out_alpha = color.data_ptr(), depth.data_ptr(), norm.data_ptr(), alpha.data_ptr()
+    a.out_extra = _ptr(extra)
+    a.radii = radii.data_ptr() if P > 0 else None
+    a.geom, a.img, a.bin, a.sort, a.ctrl = geom.data_ptr(), img.data_ptr(), binb.data_ptr(), sort.data_ptr(), ctrl.data_ptr()
+    a.capacity = capacity
+    a.num_rendered_pinned = sc.pinned.data_ptr()
+
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    n = C.c_int64(0)
+    with torch.cuda.device(dev):
+        st = lib.igs_forward(C.byref(a), stream, C.byref(n))
+        if st == N.IGS_ERR_CAPACITY:
+            capacity = int(n.value * 1.1) + 4096
+            binb = torch.empty(lib.igs_bin_bytes(capacity), **u8)
+            sort = sc.buf("sort", lib.igs_sort_bytes(capacity))
+            ctrl = sc.buf("ctrl", lib.igs_ctrl_bytes(P, capacity))
+            a.bin, a.sort, a.ctrl, a.capacity = binb.data_ptr(), sort.data_ptr(), ctrl.data_ptr(), capacity
+            st = lib.igs_forward_bin_render(C.byref(a), stream)
+        N.check(st, "forward")
+    num_rendered = int(n.value)
+    # next call with this shape: 25 % head-room over what this one needed
+    sc.capacity_hint[hint_key] = max(int(num_rendered * 1.25) + 4096, 1 << 14)
+    return num_rendered, color, depth, norm, alpha, radii, extra, geom, binb, img
+
+
+def _backward_native(bg, means3D, radii, colors_precomp, scales, rotations, extra_attrs, scale_modifier,
+                     cov3Ds_precomp, norm3Ds_precomp, viewmatrix, projmatrix, tanfovx, tanfovy,
+                     dL_dcolor, dL_ddepth, dL_dnorm, dL_dalpha, dL_dextra, sh, sh_degree, campos, geom,
+                     num_rendered, binb, img, alpha, debug):
+    """Equivalent of _C.rasterize_gaussians_backward (DGR rasterize_points.cu:135-239)."""
+    lib = N.lib()
+    dev = means3D.device
+    P = means3D.size(0)
+    H, W = alpha.size(1), alpha.size(2)
+    ED = extra_attrs.size(1) if extra_attrs.numel() != 0 else 0
+    M = sh.size(1) if sh.numel() != 0 else 0
+    sc = _get_scratch(dev)
+    # one allocation for all per-Gaussian gradients, contiguous sub-blocks
+    widths = [3, 3, 1, 3, 6, 3, 3 * M, 3, 4, ED]
+    flat = torch.empty((P * sum(widths),), dtype=torch.float32, device=dev)
+    outs, o = [], 0
+    for w in widths:
+        outs.append(flat[o:o + P * w].view(P, w))
+        o += P * w
+    (g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_norm3D, g_sh, g_scales, g_rot, g_extra) = outs
+    g_sh = g_sh.view(P, M, 3)
+    if ED == 0:
+        g_extra = torch.empty((0,), dtype=torch.float32, device=dev)
+    accum = sc.buf("accum", lib.igs_accum_bytes(P, ED))
+
+    def grad(t, C_):
+        return sc.zeros_like_img(C_, H, W) if t is None else _f32c(t)
+
+    keep = [_f32c(bg), _f32c(viewmatrix), _f32c(projmatrix), _f32c(campos), _f32c(means3D), _f32c(sh),
+            _f32c(colors_precomp), _f32c(scales), _f32c(rotations), _f32c(cov3Ds_precomp),
+            _f32c(norm3Ds_precomp), _f32c(extra_attrs), radii, geom, img, binb, _f32c(alpha),
+            grad(dL_dcolor, 3), grad(dL_ddepth, 1), grad(dL_dnorm, 3), grad(dL_dalpha, 1),
+            grad(dL_dextra, ED) if ED > 0 else None]
+    a = N.IgsBwdArgs()
+    a.P, a.D, a.M, a.ED, a.W, a.H = P, int(sh_degree), M, ED, W, H
+    a.tan_fovx, a.tan_fovy, a.scale_modifier, a.debug = tanfovx, tanfovy, scale_modifier, int(bool(debug))
+    a.num_rendered = num_rendered
+    (a.bg, a.viewmatrix, a.projmatrix, a.campos, a.means3D, a.shs, a.colors_precomp, a.scales, a.rotations,
+     a.cov3Ds_precomp, a.norm3Ds_precomp, a.extra_attrs, a.radii, a.geom, a.img, a.bin, a.out_alpha,
+     a.dL_dcolor, a.dL_ddepth, a.dL_dnorm, a.dL_dalpha, a.dL_dextra) = [_ptr(t) for t in keep]
+    a.accum = accum.data_ptr()
+    (a.dL_dmeans2D, a.dL_dcolors, a.dL_dopacity, a.dL_dmeans3D, a.dL_dcov3D, a.dL_dnorm3D, a.dL_dsh,
+     a.dL_dscales, a.dL_drotations, a.dL_dextra_attrs) = [_ptr(t) for t in
+                                                          (g_means2D, g_colors, g_opacity, g_means3D, g_cov3D,
+                                                           g_norm3D, g_sh, g_scales, g_rot, g_extra)]
+    with torch.cuda.device(dev):
+        N.check(lib.igs_backward(C.byref(a), torch.cuda.current_stream(dev).cuda_stream), "backward")
+    return g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_norm3D, g_sh, g_scales, g_rot, g_extra
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    # DGR diff_gauss/__init__.py:52-178
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                norm3Ds_precomp, extra_attrs, raster_settings):
+        assert extra_attrs.shape[0] == 0 or extra_attrs.shape[1] <= N.MAX_EXTRA_DIMS
+        args = (
+            raster_settings.bg, means3D, colors_precomp, opacities, scales, rotations,
+            raster_settings.scale_modifier, cov3Ds_precomp, norm3Ds_precomp, extra_attrs,
+            extra_attrs.shape[1] if extra_attrs.shape[0] != 0 else 0,
+            raster_settings.viewmatrix, raster_settings.projmatrix, raster_settings.tanfovx,
+            raster_settings.tanfovy, raster_settings.image_height, raster_settings.image_width, sh,
+            raster_settings.sh_degree, raster_settings.campos, raster_settings.prefiltered,
+            raster_settings.debug)
+        if raster_settings.debug:
+            cpu_args = cpu_deep_copy_tuple(args)  # copy them before they can be corrupted
+            try:
+                res = _forward_native(*args)
+            except Exception as ex:
+                torch.save(cpu_args, "snapshot_fw.dump")
+                print("\nAn error occured in forward. Please forward snapshot_fw.dump for debugging.")
+                raise ex
+        else:
+            res = _forward_native(*args)
+        num_rendered, color, depth, norm, alpha, radii, extra, geomBuffer, binningBuffer, imgBuffer = res
+        ctx.raster_settings = raster_settings
+        ctx.num_rendered = num_rendered
+        ctx.set_materialize_grads(False)
+        ctx.mark_non_differentiable(radii)
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, norm3Ds_precomp,
+                              radii, extra_attrs, sh, geomBuffer, binningBuffer, imgBuffer, alpha)
+        return color, depth, norm, alpha, radii, extra
+
+    @staticmethod
+    def backward(ctx, grad_out_color, grad_out_depth, grad_out_norm, grad_out_alpha, _, grad_out_extra):
+        num_rendered = ctx.num_rendered
+        raster_settings = ctx.raster_settings
+        (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, norm3Ds_precomp, radii, extra_attrs, sh,
+         geomBuffer, binningBuffer, imgBuffer, alpha) = ctx.saved_tensors
+        args = (raster_settings.bg, means3D, radii, colors_precomp, scales, rotations, extra_attrs,
+                raster_settings.scale_modifier, cov3Ds_precomp, norm3Ds_precomp, raster_settings.viewmatrix,
+                raster_settings.projmatrix, raster_settings.tanfovx, raster_settings.tanfovy, grad_out_color,
+                grad_out_depth, grad_out_norm, grad_out_alpha, grad_out_extra, sh, raster_settings.sh_degree,
+                raster_settings.campos, geomBuffer, num_rendered, binningBuffer, imgBuffer, alpha,
+                raster_settings.debug)
+        if raster_settings.debug:
+            cpu_args = cpu_deep_copy_tuple(args)
+            try:
+                res = _backward_native(*args)
+            except Exception as ex:
+                torch.save(cpu_args, "snapshot_bw.dump")
+                print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
+                raise ex
+        else:
+            res = _backward_native(*args)
+        (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp,
+         grad_norm3Ds_precomp, grad_sh, grad_scales, grad_rotations, grad_extra_attrs) = res
+        grads = (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales,
+                 grad_rotations, grad_cov3Ds_precomp, grad_norm3Ds_precomp, grad_extra_attrs, None)
+        # gradients for inputs that do not require one (incl. the empty 'None'
+        # sentinels) are dropped, as autograd would do with the reference's
+        return tuple(g if (g is not None and need) else None for g, need in zip(grads, ctx.needs_input_grad))
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                        norm3Ds_precomp, extra_attrs, raster_settings):
+    # DGR diff_gauss/__init__.py:21-50
+    color, depth, norm, alpha, radii, extra = _RasterizeGaussians.apply(
+        means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, norm3Ds_precomp,
+        extra_attrs, raster_settings)
+    norm = torch.nn.functional.normalize(norm, p=2, dim=0)
+    return color, depth, norm, alpha, radii, extra
+
+
+class GaussianRasterizer(nn.Module):
+    # DGR diff_gauss/__init__.py:194-250
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        with torch.no_grad():
+            rs = self.raster_settings
+            if not positions.is_cuda:
+                raise RuntimeError("libigs_raster is CUDA-only: positions must be a CUDA tensor")
+            pos, view, proj = _f32c(positions), _f32c(rs.viewmatrix), _f32c(rs.projmatrix)
+            P = pos.size(0)
+            visible = torch.empty((P,), dtype=torch.bool, device=pos.device)
+            if P:
+                with torch.cuda.device(pos.device):
+                    N.check(N.lib().igs_mark_visible(P, pos.data_ptr(), view.data_ptr(), proj.data_ptr(),
+                                                     visible.data_ptr(),
+                                                     torch.cuda.current_stream(pos.device).cuda_stream),
+                            "mark_visible")
+        return visible
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                cov3Ds_precomp=None, norm3Ds_precomp=None, extra_attrs=None):
+        raster_settings = self.raster_settings
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        if ((scales is None or rotations is None) and cov3Ds_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3Ds_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        if shs is None:
+            shs = torch.Tensor([])
+        if colors_precomp is None:
+            colors_precomp = torch.Tensor([])
+        if scales is None:
+            raise ValueError('To support norm and depth prediction, scales == None is not allowed')
+        if rotations is None:
+            raise ValueError('To support norm and depth prediction, rotations == None is not allowed')
+        if cov3Ds_precomp is None:
+            cov3Ds_precomp = torch.Tensor([])
+        if norm3Ds_precomp is None:
+            norm3Ds_precomp = torch.Tensor([])
+        if extra_attrs is None:
+            extra_attrs = torch.Tensor([])
+        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
+                                   cov3Ds_precomp, norm3Ds_precomp, extra_attrs, raster_settings)

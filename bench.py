@@ -1,0 +1,439 @@
+#!/usr/bin/env python
+"""Benchmark of the rasterizer hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl igs|reference]
+
+One "step" = one forward+backward rasterization of the BASELINE config-2 frame
+(P=100k Gaussians, 512x512, precomputed colours, ED=1, gradients into colour,
+depth, normal, alpha and extra) on synthetic seeded inputs.  N>1: one process
+per GPU (torchrun), every rank renders its own camera of the same cloud
+(view-sharded batch) and the packed per-Gaussian gradients are summed with one
+NCCL all-reduce per step; value = N frames / max-over-ranks step time.
+
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every field.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "rasterizer fwd+bwd frames/sec @512^2 ~100k Gaussians"
+L2_FLUSH_BYTES = 256 << 20  # > 126 MB L2
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="igs", choices=["igs", "reference"])
+    ap.add_argument("--workload", default="C2", choices=["C2", "C3_face", "C3_mouth", "C1", "C5"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--no-synth", action="store_true", help="skip the auxiliary forward-only synthesis fps")
+    return ap.parse_args()
+
+
+class ClockSampler(threading.Thread):
+    """SM clock + throttle reasons of this rank's GPU while the timed region runs (NVML)."""
+
+    def __init__(self, index, period=0.02):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.stop_flag = [], set(), False
+        self.sm_max = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and vis.split(",")[index].isdigit() else index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def result(self):
+        self.stop_flag = True
+        if self.nv is None or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.sm_max, "reasons": ["nvml unavailable"]}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.sm_max,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def algorithmic_bytes(P, N, HW, T, S=0, c=0, ED=1, passes=6):
+    """SURVEY.md 8(d) per-stage algorithmic bytes, with this library's record sizes:
+    preprocess reads 44(+12S) B and writes the 64 B splat record + radii/tiles/offsets (+1 clamp);
+    sort = (8+4) B read + written per pass (+ the duplicate's first write is in `duplicate`)."""
+    return {
+        "preprocess": (44 + 12 * S + 64 + 12 + c) * P,
+        "duplicate": 20 * P + 12 * N,
+        "sort": passes * 24 * N,
+        "tile_ranges": 8 * N + 8 * T,
+        "render": (4 + 64) * N + (4 * (8 + ED) + 4) * HW,
+        "render_backward": (4 + 64) * N + (8 + 4 * (8 + ED)) * HW + 2 * 64 * P,
+        "preprocess_backward": (64 + 64 + 44 + 12 * S + c + 4 * (26 + 3 * (S if S else 0) + ED)) * P,
+    }
+
+
+# ---------------------------------------------------------------------------
+# the two arms: same call shapes, different library underneath
+# ---------------------------------------------------------------------------
+class Arm:
+    """fwd+bwd of one frame, (a) raw through the native entry points with device-resident inputs
+    and fixed upstream gradients, (b) end to end: pinned host inputs -> H2D -> module API -> loss ->
+    backward -> D2H of the loss."""
+
+    def __init__(self, impl, sc, grads, device):
+        import torch
+        import util as U
+        self.torch, self.U, self.impl, self.device = torch, U, impl, device
+        self.sc = sc
+        self.t = U.to_torch(sc, device)
+        self.tg = {k: torch.from_numpy(v).to(device) for k, v in grads.items()}
+        self.ED = sc["extra_attrs"].shape[1] if sc.get("extra_attrs") is not None else 0
+        if impl == "igs":
+            from instag_b200 import rasterizer as R
+            from diff_gauss import GaussianRasterizer
+            self.fwd_raw, self.bwd_raw, self.Module = R._forward_native, R._backward_native, GaussianRasterizer
+        else:
+            from oracle import ref_cuda as RC
+            self.fwd_raw, self.bwd_raw, self.Module = RC.forward_raw, RC.backward_raw, RC.RefGaussianRasterizer
+        self.fargs = U.raw_args_fwd(self.t)
+        self.rs = U.settings_from(self.t)
+        # pinned host copies of the per-frame inputs (what a training step receives from its data side)
+        self.names = [k for k in ("means3D", "opacities", "scales", "rotations", "shs", "colors_precomp",
+                                  "extra_attrs") if self.t.get(k) is not None]
+        self.host = {k: self.t[k].cpu().pin_memory() for k in self.names}
+        self.h2d_bytes = sum(v.numel() * 4 for v in self.host.values())
+        self.loss_host = torch.zeros(1).pin_memory()
+        self.last = None
+
+    def step_raw(self):
+        n, color, depth, norm, alpha, radii, extra, geom, binb, img = self.fwd_raw(*self.fargs)
+        res = self.bwd_raw(*self.U._bwd_args(self.t, radii, self.tg, geom, n, binb, img, alpha))
+        self.last = (n, res, radii)
+        return res
+
+    def step_fwd_only(self):
+        return self.fwd_raw(*self.fargs)
+
+    def step_e2e(self):
+        torch = self.torch
+        dev = {k: v.to(self.device, non_blocking=True) for k, v in self.host.items()}
+        leaves = {k: dev[k].requires_grad_(True) for k in dev}
+        m2 = torch.zeros_like(dev["means3D"], requires_grad=True)
+        color, depth, norm, alpha, radii, extra = self.Module(self.rs)(
+            means3D=leaves["means3D"], means2D=m2, shs=leaves.get("shs"),
+            colors_precomp=leaves.get("colors_precomp"), opacities=leaves["opacities"], scales=leaves["scales"],
+            rotations=leaves["rotations"], extra_attrs=leaves.get("extra_attrs"))
+        g = self.tg
+        loss = (color * g["color"]).sum() + (depth * g["depth"]).sum() + (norm * g["norm"]).sum() + \
+            (alpha * g["alpha"]).sum()
+        if self.ED:
+            loss = loss + (extra * g["extra"]).sum()
+        loss.backward()
+        self.loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+        return leaves, m2
+
+
+def timed(torch, dist, step, steps, warmup, flush, world):
+    """W untimed + EXACTLY K timed steps; CUDA events per step on the current stream, L2 flushed
+    between steps outside the event pairs; barrier + synchronize on both sides; max over ranks."""
+    for _ in range(warmup):
+        flush.zero_()
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    t0 = time.perf_counter()
+    for s, e in ev:
+        flush.zero_()
+        s.record()
+        step()
+        e.record()
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    per = np.array([s.elapsed_time(e) for s, e in ev])
+    ms = float(per.sum() / steps)
+    if world > 1:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms, per, wall
+
+
+def cpu_baseline(sc, grads, seconds, backward=True):
+    """The CPU restatement (oracle/, kind "port": the reference has no CPU rasterizer) on the box's
+    host cores, whole frames of the same workload until ~`seconds` of CPU work."""
+    import util as U
+    from oracle import cpu_oracle as O
+    s = U.oracle_scene(sc)
+    f = O.forward(s)  # warm (also: pair counts for the FP32 roofline)
+    n, t0 = 0, time.perf_counter()
+    while True:
+        f = O.forward(s, want_border=False)
+        if backward:
+            O.backward(s, f, grads["color"], grads["depth"], grads["norm"], grads["alpha"], grads.get("extra"))
+        n += 1
+        el = time.perf_counter() - t0
+        if el >= seconds or n >= 50:
+            break
+    return {"value": n / el, "unit": "frames/s", "cores": O.num_threads(), "kind": "port",
+            "sample": f"{n} whole frame(s) of the same workload (fwd{'+bwd' if backward else ''}) in {el:.1f} s, "
+                      f"C restatement oracle/*.c with OpenMP over tiles/Gaussians"}, f
+
+
+def main():
+    a = parse()
+    import torch
+    import torch.distributed as dist
+    import util as U
+    from instag_b200 import synthetic as S
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if a.impl == "reference" and rank != 0:
+        return  # the reference arm is a single-GPU number: rank 0 alone runs it
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1 and a.impl == "igs":
+        dist.init_process_group("nccl", device_id=device)
+    eff_world = world if a.impl == "igs" else 1
+
+    cfg = dict(S.CONFIGS[a.workload])
+    cloud = S.make_cloud(cfg["P"], sh_degree=cfg["sh_degree"], M=cfg["M"] or None, seed=0)
+    cams = S.camera_sequence(max(eff_world, 1), cfg["W"], cfg["H"], seed=0)
+    cam = S.make_camera(cfg["W"], cfg["H"]) if eff_world == 1 else cams[rank]
+    sc = dict(cloud)
+    sc.update(cam)
+    sc["bg"] = np.asarray(cfg["bg"], np.float32)
+    grads = S.upstream_grads(cfg["H"], cfg["W"], extra_dims=1, seed=1)
+    backward = cfg["backward"]
+    P, H, W = cfg["P"], cfg["H"], cfg["W"]
+
+    if a.impl == "reference":
+        from oracle import ref_cuda
+        if not ref_cuda.available():
+            return reference_cpu_arm(a, sc, grads, backward, cfg)
+    arm = Arm(a.impl, sc, grads, device)
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=device)
+
+    def step():
+        if not backward:
+            return arm.step_fwd_only()
+        res = arm.step_raw()
+        if eff_world > 1:
+            dist.all_reduce(res[0]._base if res[0]._base is not None else res[0])  # packed per-Gaussian grads
+        return res
+
+    def step_e2e():
+        out = arm.step_e2e()
+        if eff_world > 1:
+            for v in out[0].values():
+                dist.all_reduce(v.grad)
+        return out
+
+    if a.impl == "igs":
+        from instag_b200 import _native as NV
+    sampler = ClockSampler(local)
+    # ---- device-resident timing (value) ----
+    for _ in range(2):
+        step()
+    torch.cuda.synchronize()
+    if a.impl == "igs":
+        NV.profile_enable(True)
+        # warm-up happens inside timed(); the ring keeps the last 256 frames = timed ones when K<=256
+    sampler.start()
+    ms, per, wall = timed(torch, dist, step, a.steps, a.warmup, flush, eff_world)
+    clocks = sampler.result()
+    stages, frames = ({}, 0)
+    if a.impl == "igs":
+        stages, frames = NV.profile_read()
+        NV.profile_enable(False)
+        l0 = NV.launch_count()
+        step()
+        torch.cuda.synchronize()
+        launches_per_step = NV.launch_count() - l0
+    N = int(arm.last[0]) if arm.last else int(arm.step_fwd_only()[0])
+    value = eff_world * 1000.0 / ms
+
+    # ---- end to end (host buffers, H2D + D2H inside the timed region) ----
+    if backward:
+        ms_e2e, _, _ = timed(torch, dist, step_e2e, a.steps, max(a.warmup, 3), flush, eff_world)
+        e2e = {"value": eff_world * 1000.0 / ms_e2e, "unit": "frames/s", "h2d_bytes_per_step": arm.h2d_bytes,
+               "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e,
+               "path": "pinned host inputs -> H2D -> GaussianRasterizer(...) -> weighted-sum loss -> backward -> loss D2H"}
+    else:
+        e2e = {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+
+    line = finish(a, cfg, sc, grads, arm, eff_world, rank, ms, per, wall, value, e2e, clocks, stages, frames, N,
+                  launches_per_step if a.impl == "igs" else 0, backward, torch, dist, flush)
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1 and a.impl == "igs":
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)", d
+    return 6650.0, "fallback (B200_PROFILING.md)", {}
+
+
+def finish(a, cfg, sc, grads, arm, world, rank, ms, per, wall, value, e2e, clocks, stages, frames, N, launches,
+           backward, torch, dist, flush):
+    P, H, W = cfg["P"], cfg["H"], cfg["W"]
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    S_ = (cfg["sh_degree"] + 1) ** 2 if cfg["sh_degree"] is not None else 0
+    hbm_peak, peak_src, _ = load_peaks()
+    line = {
+        "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "impl": a.impl,
+        "config": {"workload": f"{a.workload}: P={P} Gaussians, {W}x{H}, "
+                               f"{'precomputed colours' if S_ == 0 else 'SH deg %d M=%d' % (cfg['sh_degree'], cfg['M'])}"
+                               f", ED=1, {'forward+backward' if backward else 'forward only'}, one camera per rank",
+                   "num_rendered": N, "frames_per_step": world,
+                   "parallelism": "single GPU" if world == 1 else f"view-sharded dp{world} + NCCL all-reduce of packed "
+                                                                  f"per-Gaussian grads",
+                   "l2": "flushed between steps (256 MiB memset outside the per-step event pairs)",
+                   "timing": "sum of per-step CUDA-event pairs / K, max over ranks"},
+        "e2e": e2e, "clocks": clocks, "wall_s_timed_region": wall,
+        "ms_per_step_p10_p50_p90": [float(np.percentile(per, q)) for q in (10, 50, 90)],
+        "gpu_launches": int(launches) * a.steps,
+        "gpu_launches_per_step": int(launches),
+    }
+    if a.impl == "reference":
+        line["cpu_baseline"] = {"value": value, "unit": "frames/s", "cores": 0, "kind": "reference",
+                                "sample": "the UNMODIFIED reference CUDA rasterizer (oracle/_ref/libdgr_ref.so, "
+                                          "compiled for sm_100a) on the same GPU, whole frames; the reference has "
+                                          "no CPU implementation of this path"}
+        return line
+    # ---- roofline of the dominant kernel + per-stage table ----
+    alg = algorithmic_bytes(P, N, H * W, T, S=S_, c=1 if S_ else 0)
+    table = {}
+    for k, t in stages.items():
+        if t is None or t <= 0:
+            continue
+        gbs = alg[k] / (t * 1e-3) / 1e9
+        table[k] = {"ms": t, "alg_bytes": int(alg[k]), "gbs": gbs, "frac_hbm": gbs / hbm_peak}
+    if table:
+        dom = max(table, key=lambda k: table[k]["ms"])
+        d = table[dom]
+        line["roofline"] = {"kernel": dom, "bound": "hbm", "achieved": d["gbs"], "peak": hbm_peak, "unit": "GB/s",
+                            "frac": d["frac_hbm"], "traffic": None, "peak_source": peak_src,
+                            "alg_bytes_per_launch": d["alg_bytes"], "ms_per_launch": d["ms"],
+                            "frames_averaged": frames,
+                            "share_of_step": d["ms"] / sum(v["ms"] for v in table.values()),
+                            "note": "render / render_backward are FP32-issue bound, not HBM bound: see fp32"}
+        line["stages"] = table
+        line["stage_ms_sum"] = sum(v["ms"] for v in table.values())
+    # ---- CPU baseline (rank 0, N=1 only) + pair counts for the FP32 model ----
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        cb, f = cpu_baseline(sc, grads, a.cpu_seconds, backward)
+        line["cpu_baseline"] = cb
+        q_eval, q_acc = f["pairs_evaluated"], f["pairs_blended"]
+        q_eval_b = int(np.asarray(f["n_contrib"], np.int64).sum())
+        sm_mhz = clocks.get("sm_mhz") or 1965.0
+        fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12
+        fp = {"pairs_evaluated": q_eval, "pairs_blended": q_acc, "pairs_evaluated_backward": q_eval_b,
+              "peak_tflops_at_observed_clock": fp32_peak,
+              "model": "fwd 15*Q_eval + 17*Q_acc, bwd 15*Q_eval' + 110*Q_acc flop (SURVEY 8d)"}
+        if "render" in table:
+            fl = 15 * q_eval + 17 * q_acc
+            fp["render_tflops"] = fl / (table["render"]["ms"] * 1e-3) / 1e12
+            fp["render_frac"] = fp["render_tflops"] / fp32_peak
+        if "render_backward" in table:
+            fl = 15 * q_eval_b + 110 * q_acc
+            fp["render_backward_tflops"] = fl / (table["render_backward"]["ms"] * 1e-3) / 1e12
+            fp["render_backward_frac"] = fp["render_backward_tflops"] / fp32_peak
+        line["fp32"] = fp
+    # ---- auxiliary: forward-only synthesis fps (face 100k + mouth 30k per frame, frames sharded, no collective) ----
+    if not a.no_synth and a.workload == "C2":
+        line["synth"] = synth_fps(torch, dist, world, rank, flush, arm.device)
+    return line
+
+
+def synth_fps(torch, dist, world, rank, flush, device, frames=60):
+    """BASELINE config 4 shape: per frame one face (100k, SH deg 1 M=4) + one mouth (30k) forward
+    rasterization; every rank renders its own frames (different cameras), no collective."""
+    import util as U
+    from instag_b200 import synthetic as S
+    from instag_b200 import rasterizer as R
+    cams = S.camera_sequence(frames * world, 512, 512, seed=3)[rank::world]
+    clouds = [S.make_cloud(100_000, sh_degree=1, M=4, seed=0), S.make_cloud(30_000, sh_degree=1, M=4, seed=1)]
+    tcl = [U.to_torch(c, device) for c in clouds]
+    scenes = []
+    for cam in cams:
+        tc = U.to_torch(dict(cam, bg=np.zeros(3, np.float32)), device)
+        scenes.append([U.raw_args_fwd({**cl, **tc}) for cl in tcl])
+    it = iter(range(10 ** 9))
+
+    def step():
+        i = next(it) % len(scenes)
+        face = R._forward_native(*scenes[i][0])
+        mouth = R._forward_native(*scenes[i][1])
+        # synthesize_fuse.py:70-74 composition
+        return face[1] + mouth[1] * (1.0 - face[4])
+
+    ms, _, _ = timed(torch, dist, step, frames, 5, flush, world)
+    return {"value": world * 1000.0 / ms, "unit": "frames/s", "ms_per_frame": ms,
+            "workload": "face 100k + mouth 30k Gaussians (SH deg 1, M=4), 512x512, forward only + compose; "
+                        "frames sharded over ranks, no collective"}
+
+
+def reference_cpu_arm(a, sc, grads, backward, cfg):
+    """Fallback of --impl reference when the compiled reference is absent: the CPU port."""
+    cb, _ = cpu_baseline(sc, grads, max(a.cpu_seconds, 10.0), backward)
+    v = cb["value"]
+    print(json.dumps({"metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": 1, "steps": a.steps,
+                      "warmup": a.warmup, "ms_per_step": 1000.0 / v, "higher_is_better": True, "scaling": "weak",
+                      "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
+                      "config": {"workload": a.workload}, "cpu_baseline": cb,
+                      "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+if __name__ == "__main__":
+    main()

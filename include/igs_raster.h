@@ -168,6 +168,20 @@ int igs_forward_bin_render(const IgsFwdArgs* args, igs_stream_t stream);
 
 int igs_backward(const IgsBwdArgs* args, igs_stream_t stream);
 
+/* Measurement hooks (no reference counterpart; SURVEY.md 5 "tracing").  With
+ * profiling enabled the library records CUDA events on the launching stream at
+ * the stage boundaries of every igs_forward / igs_backward of this host
+ * thread (a ring of the last 256 frames); igs_profile_read waits for them and
+ * returns the MEAN stage durations in ms over the *frames recorded since
+ * igs_profile_enable(1) (-1 = stage did not run): 0 preprocess+scan, 1 duplicate (+ the 4-byte
+ * num_rendered copy), 2 radix sort (all passes), 3 tile ranges, 4 render,
+ * 5 render backward, 6 per-Gaussian backward.  igs_launch_count returns how
+ * many kernels this host thread has launched through the library so far. */
+#define IGS_NUM_STAGES 7
+int igs_profile_enable(int on);
+int igs_profile_read(float* ms /* [IGS_NUM_STAGES] */, int32_t* frames);
+uint64_t igs_launch_count(void);
+
 int igs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
                      const float* projmatrix, uint8_t* present, igs_stream_t stream);
 

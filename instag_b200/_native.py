@@ -68,6 +68,9 @@ SYMBOLS = {
     "igs_forward": (C.c_int, [C.POINTER(IgsFwdArgs), _p, C.POINTER(C.c_int64)]),
     "igs_forward_bin_render": (C.c_int, [C.POINTER(IgsFwdArgs), _p]),
     "igs_backward": (C.c_int, [C.POINTER(IgsBwdArgs), _p]),
+    "igs_profile_enable": (C.c_int, [C.c_int]),
+    "igs_profile_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
+    "igs_launch_count": (C.c_uint64, []),
     "igs_mark_visible": (C.c_int, [C.c_int32, _p, _p, _p, _p, _p]),
 }
 
@@ -98,6 +101,27 @@ def last_error():
 def check(status, what):
     if status != IGS_OK:
         raise RuntimeError(f"libigs_raster {what} failed ({status}): {last_error()}")
+
+
+NUM_STAGES = 7
+STAGE_NAMES = ("preprocess", "duplicate", "sort", "tile_ranges", "render", "render_backward",
+               "preprocess_backward")
+
+
+def profile_enable(on=True):
+    lib().igs_profile_enable(int(bool(on)))
+
+
+def profile_read():
+    """(mean stage durations in ms since profile_enable, frames averaged); waits for the events."""
+    ms = (C.c_float * NUM_STAGES)()
+    n = C.c_int32(0)
+    check(lib().igs_profile_read(ms, C.byref(n)), "profile_read")
+    return dict(zip(STAGE_NAMES, [float(x) for x in ms])), int(n.value)
+
+
+def launch_count():
+    return int(lib().igs_launch_count())
 
 
 def geom_layout(P):

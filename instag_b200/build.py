@@ -26,11 +26,23 @@ def _deps():
     return out
 
 
+STAMP = os.path.join(HERE, "libigs_raster.stamp")
+
+
+def _digest():
+    """Content hash of every source (mtimes do not survive the copy to the GPU box)."""
+    import hashlib
+    h = hashlib.sha256(" ".join(FLAGS).encode())
+    for p in sorted(_deps()):
+        if p.endswith((".cu", ".cuh", ".h")):
+            h.update(open(p, "rb").read())
+    return h.hexdigest()
+
+
 def needs_build():
-    if not os.path.exists(LIB):
+    if not os.path.exists(LIB) or not os.path.exists(STAMP):
         return True
-    t = os.path.getmtime(LIB)
-    return any(os.path.getmtime(p) > t for p in _deps())
+    return open(STAMP).read().strip() != _digest()
 
 
 def _compile(src):
@@ -58,6 +70,8 @@ def build(force=False, verbose=False):
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
     with open(os.path.join(CSRC, "ptxas.log"), "w") as f:
         f.write("\n".join(log))
+    with open(STAMP, "w") as f:
+        f.write(_digest())
     if verbose:
         print("\n".join(log))
     return LIB

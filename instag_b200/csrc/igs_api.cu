@@ -32,6 +32,33 @@ int stage_check(bool debug, cudaStream_t s, const char* what) {
   return check_cuda(e, what);
 }
 
+// ---- profiling: CUDA events on the launching stream, only when enabled -------
+constexpr int PROF_RING = 256; // frames kept; older ones are overwritten
+struct Profiler {
+  bool enabled = false;
+  int slot = -1;        // frame being recorded (advanced at boundary 0)
+  long long frames = 0; // frames started since enable
+  bool have[PROF_RING][PROF_BOUNDARIES] = {};
+  cudaEvent_t ev[PROF_RING][PROF_BOUNDARIES] = {};
+};
+static thread_local Profiler g_prof;
+static thread_local unsigned long long g_launches = 0;
+
+void prof_mark(int b, cudaStream_t s) {
+  Profiler& p = g_prof;
+  if (!p.enabled) return;
+  if (b == 0) {
+    p.slot = (p.slot + 1) % PROF_RING;
+    p.frames++;
+    for (int k = 0; k < PROF_BOUNDARIES; k++) p.have[p.slot][k] = false;
+  }
+  if (p.slot < 0) return;
+  cudaEvent_t& e = p.ev[p.slot][b];
+  if (!e) cudaEventCreate(&e);
+  p.have[p.slot][b] = cudaEventRecord(e, s) == cudaSuccess;
+}
+void count_launch(int n) { g_launches += (unsigned long long)n; }
+
 static int num_passes(int grid_x, int grid_y) {
   const int bits = 32 + higher_msb((uint32_t)(grid_x * grid_y)); // reference rasterizer_impl.cu:303-311
   return (bits + RADIX_BITS - 1) / RADIX_BITS;
@@ -140,6 +167,7 @@ static int run_bin_render(const IgsFwdArgs* a, cudaStream_t s) {
   ra.out_alpha = a->out_alpha; ra.out_extra = a->out_extra;
   ra.n_contrib = (uint32_t*)(im + il.n_contrib);
   launch_render(ra, s);
+  prof_mark(5, s);
   return stage_check(debug, s, "render");
 }
 
@@ -199,7 +227,9 @@ int igs_forward(const IgsFwdArgs* a, igs_stream_t stream, int64_t* num_rendered)
     return stage_check(debug, s, "empty forward");
   }
   const PreArgs pa = make_pre(a);
+  prof_mark(0, s);
   launch_preprocess(pa, s);
+  prof_mark(1, s);
   if (int r = stage_check(debug, s, "preprocess")) return r;
   if (int r = check_cuda(cudaMemcpyAsync(a->num_rendered_pinned, &pa.header->num_rendered, sizeof(int32_t),
                                          cudaMemcpyDeviceToHost, s), "copy num_rendered")) return r;
@@ -256,7 +286,9 @@ int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
   ra.dL_dalpha = a->dL_dalpha; ra.dL_dextra = a->dL_dextra;
   ra.accum = (float*)a->accum;
   ra.accum_extra = a->ED > 1 ? (float*)((char*)a->accum + align_up((size_t)a->P * ACC_F * sizeof(float))) : nullptr;
+  prof_mark(6, s);
   if (a->num_rendered > 0) launch_render_backward(ra, s);
+  prof_mark(7, s);
   if (int r = stage_check(debug, s, "render backward")) return r;
 
   BwdPreArgs pa{};
@@ -276,8 +308,44 @@ int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
   pa.dL_dsh = a->dL_dsh; pa.dL_dscales = a->dL_dscales; pa.dL_drotations = a->dL_drotations;
   pa.dL_dextra_attrs = a->dL_dextra_attrs;
   launch_preprocess_backward(pa, s);
+  prof_mark(8, s);
   return stage_check(debug, s, "preprocess backward");
 }
+
+int igs_profile_enable(int on) {
+  Profiler& p = g_prof;
+  p.enabled = on != 0;
+  p.slot = -1;
+  p.frames = 0;
+  for (int f = 0; f < PROF_RING; f++)
+    for (int k = 0; k < PROF_BOUNDARIES; k++) p.have[f][k] = false;
+  return IGS_OK;
+}
+
+int igs_profile_read(float* ms, int32_t* frames) {
+  if (!ms) { set_error("null ms"); return IGS_ERR_INVALID; }
+  Profiler& p = g_prof;
+  // stage k = boundary k -> k+1, except 5->6 (between forward and backward)
+  static const int from[IGS_NUM_STAGES] = {0, 1, 2, 3, 4, 6, 7};
+  int used = 0;
+  for (int k = 0; k < IGS_NUM_STAGES; k++) {
+    double sum = 0.0;
+    int n = 0;
+    const int a = from[k], b = a + 1;
+    for (int f = 0; f < PROF_RING; f++) {
+      if (!p.have[f][a] || !p.have[f][b]) continue;
+      if (int r = check_cuda(cudaEventSynchronize(p.ev[f][b]), "profile sync")) return r;
+      float t = 0.f;
+      if (cudaEventElapsedTime(&t, p.ev[f][a], p.ev[f][b]) == cudaSuccess) { sum += t; n++; }
+    }
+    ms[k] = n ? (float)(sum / n) : -1.f;
+    if (n > used) used = n;
+  }
+  if (frames) *frames = used;
+  return IGS_OK;
+}
+
+uint64_t igs_launch_count(void) { return g_launches; }
 
 int igs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, igs_stream_t stream) {

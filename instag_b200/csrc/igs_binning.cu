@@ -239,15 +239,19 @@ void launch_binning(const BinArgs& a, cudaStream_t s) {
   }
   const int dup_blocks = (int)((a.capacity + DUP_TILE - 1) / DUP_TILE);
   duplicate_kernel<<<dup_blocks, DUP_THREADS, 0, s>>>(a);
+  prof_mark(2, s);
   for (int p = 0; p < a.passes; p++) {
     const int in = p & 1, out = in ^ 1;
     onesweep_kernel<<<a.sort_blocks, SORT_THREADS, 0, s>>>(a.keys[in], a.vals[in], a.keys[out], a.vals[out],
                                                            a.hist, a.lookback + (size_t)p * a.sort_blocks * RADIX,
                                                            a.header, p, a.capacity);
   }
+  prof_mark(3, s);
   const uint64_t* sorted = a.keys[a.passes & 1];
   const int64_t threads = a.capacity + 1 > a.num_tiles ? a.capacity + 1 : a.num_tiles;
   tile_ranges_kernel<<<(int)((threads + 255) / 256), 256, 0, s>>>(sorted, a.header, a.capacity, a.ranges, a.num_tiles);
+  prof_mark(4, s);
+  count_launch(2 + a.passes);
 }
 
 } // namespace igs

@@ -126,6 +126,14 @@ void set_error(const char* fmt, ...);
 int check_cuda(cudaError_t e, const char* what);
 int stage_check(bool debug, cudaStream_t s, const char* what);
 
+// optional per-stage timing + launch accounting (igs_api.cu; include/igs_raster.h
+// igs_profile_*).  Boundaries: 0 fwd start | 1 preprocess done | 2 duplicate done |
+// 3 sort done | 4 ranges done | 5 render done | 6 bwd start | 7 render-backward done |
+// 8 per-Gaussian backward done.
+constexpr int PROF_BOUNDARIES = 9;
+void prof_mark(int boundary, cudaStream_t s);
+void count_launch(int n = 1);
+
 // ---- device helpers ---------------------------------------------------------
 // a0*b0 + a1*b1 + a2*b2 with the contraction nvcc applies to that expression
 // (left product of the first sum fused, see DESIGN.md "FMA contraction");

@@ -243,11 +243,13 @@ void launch_preprocess(const PreArgs& a, cudaStream_t s) {
   const int blocks = (a.P + PRE_THREADS - 1) / PRE_THREADS;
   if (a.shs) preprocess_kernel<true><<<blocks, PRE_THREADS, 0, s>>>(a);
   else preprocess_kernel<false><<<blocks, PRE_THREADS, 0, s>>>(a);
+  count_launch();
 }
 
 void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s) {
   if (P <= 0) return;
   mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, view, present);
+  count_launch();
 }
 
 } // namespace igs

@@ -265,6 +265,7 @@ void launch_preprocess_backward(const BwdPreArgs& a, cudaStream_t s) {
   const int blocks = (a.P + 255) / 256;
   if (a.shs) preprocess_backward_kernel<true><<<blocks, 256, 0, s>>>(a);
   else preprocess_backward_kernel<false><<<blocks, 256, 0, s>>>(a);
+  count_launch();
 }
 
 } // namespace igs

@@ -124,6 +124,7 @@ void launch_render(const RenderArgs& a, cudaStream_t s) {
   if (a.ED == 0) render_kernel<0><<<grid, TILE_PIX, 0, s>>>(a);
   else if (a.ED == 1) render_kernel<1><<<grid, TILE_PIX, 0, s>>>(a);
   else render_kernel<-1><<<grid, TILE_PIX, 0, s>>>(a);
+  count_launch();
 }
 
 } // namespace igs

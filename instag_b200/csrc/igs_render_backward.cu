@@ -194,6 +194,7 @@ void launch_render_backward(const BwdRenderArgs& a, cudaStream_t s) {
   if (a.ED == 0) render_backward_kernel<0><<<grid, TILE_PIX, 0, s>>>(a);
   else if (a.ED == 1) render_backward_kernel<1><<<grid, TILE_PIX, 0, s>>>(a);
   else render_backward_kernel<-1><<<grid, TILE_PIX, 0, s>>>(a);
+  count_launch();
 }
 
 } // namespace igs

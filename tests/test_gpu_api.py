@@ -1,0 +1,137 @@
+"""Drop-in API behaviour on the GPU: the keyword call gaussian_renderer makes,
+autograd plumbing, edge cases (P=0, everything culled, capacity regrowth,
+non-contiguous inputs, markVisible), error texts of the reference."""
+import numpy as np
+import pytest
+import torch
+
+import util as U
+from instag_b200 import synthetic as S
+
+pytestmark = pytest.mark.gpu
+
+
+def _call(sc, requires_grad=True, use_ref=False, **over):
+    from diff_gauss import GaussianRasterizationSettings, GaussianRasterizer
+    t = U.to_torch(sc)
+    t.update(over)
+    rs = U.settings_from(t)
+    if use_ref:
+        from oracle.ref_cuda import RefGaussianRasterizer as GaussianRasterizer  # noqa: F811
+    leaves = {}
+    for k in ("means3D", "opacities", "scales", "rotations", "shs", "colors_precomp", "extra_attrs"):
+        v = t.get(k)
+        if v is not None and requires_grad:
+            v = v.clone().requires_grad_(True)
+        leaves[k] = v
+    means2D = torch.zeros_like(t["means3D"], requires_grad=requires_grad)
+    out = GaussianRasterizer(raster_settings=rs)(
+        means3D=leaves["means3D"], means2D=means2D, shs=leaves["shs"], colors_precomp=leaves["colors_precomp"],
+        opacities=leaves["opacities"], scales=leaves["scales"], rotations=leaves["rotations"], cov3Ds_precomp=None,
+        extra_attrs=leaves["extra_attrs"])
+    leaves["means2D"] = means2D
+    return out, leaves
+
+
+def _loss(out, H, W, ED=1):
+    g = S.upstream_grads(H, W, extra_dims=ED, seed=5)
+    color, depth, norm, alpha, radii, extra = out
+    l = (color * torch.from_numpy(g["color"]).cuda()).sum() + (depth * torch.from_numpy(g["depth"]).cuda()).sum()
+    l = l + (norm * torch.from_numpy(g["norm"]).cuda()).sum() + (alpha * torch.from_numpy(g["alpha"]).cuda()).sum()
+    if ED:
+        l = l + (extra * torch.from_numpy(g["extra"]).cuda()).sum()
+    return l
+
+
+def test_module_call_and_autograd_match_reference():
+    from oracle import ref_cuda
+    if not ref_cuda.available():
+        pytest.skip("reference library not built")
+    sc = U.make_scene(P=3000, W=96, H=64, sh_degree=1, M=4, scale_mult=2.0, seed=21)
+    out, lv = _call(sc)
+    rout, rlv = _call(sc, use_ref=True)
+    assert [tuple(o.shape) for o in out] == [(3, 64, 96), (1, 64, 96), (3, 64, 96), (1, 64, 96), (3000,), (1, 64, 96)]
+    assert out[4].dtype == torch.int32 and torch.equal(out[4], rout[4])
+    for a, b in zip(out[:4] + out[5:], rout[:4] + rout[5:]):
+        assert (a - b).abs().max().item() <= 1e-5
+    _loss(out, 64, 96).backward()
+    _loss(rout, 64, 96).backward()
+    assert lv["means2D"].grad.shape == (3000, 3) and (lv["means2D"].grad[:, 2] == 0).all()
+    for k in ("means3D", "means2D", "opacities", "scales", "rotations", "shs", "extra_attrs"):
+        assert U.rel_err(lv[k].grad.cpu().numpy(), rlv[k].grad.cpu().numpy()) <= 2e-4, k
+
+
+def test_no_grad_and_detached_inputs():
+    sc = U.make_scene(P=500, W=48, H=48, seed=22)
+    with torch.no_grad():
+        out, _ = _call(sc, requires_grad=False)
+    assert not out[0].requires_grad
+    out, lv = _call(sc)
+    out[0].sum().backward()  # only the colour head receives gradient: others are None -> zeros
+    assert lv["means3D"].grad is not None and torch.isfinite(lv["means3D"].grad).all()
+
+
+def test_empty_cloud_and_all_culled():
+    sc = U.make_scene(P=0, W=40, H=24, seed=1)
+    o = U.run_igs(sc)
+    # reference rasterize_points.cu:93: with P == 0 nothing runs, outputs keep their zero fill (not bg)
+    assert o["num_rendered"] == 0 and (o["alpha"] == 0).all() and (o["color"] == 0).all()
+    sc = U.make_scene(P=777, W=40, H=24, seed=1)
+    sc["means3D"] = sc["means3D"] + np.array([0, 0, -5.0], np.float32)
+    g = S.upstream_grads(24, 40)
+    o = U.run_igs(sc, grads=g)
+    assert o["num_rendered"] == 0 and (o["radii"] == 0).all() and (o["alpha"] == 0).all()
+    assert np.allclose(o["color"], np.asarray(sc["bg"]).reshape(3, 1, 1))
+    for k in U.GRAD_NAMES:
+        assert (o[k] == 0).all(), k
+
+
+def test_capacity_regrowth_gives_identical_result():
+    from instag_b200 import rasterizer as R
+    sc = U.make_scene(P=3000, W=128, H=128, scale_mult=6.0, seed=23)
+    a = U.run_igs(sc)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    R._get_scratch(dev).capacity_hint[(3000, 128, 128)] = 1000   # far too small: forces IGS_ERR_CAPACITY
+    b = U.run_igs(sc)
+    assert a["num_rendered"] == b["num_rendered"] > 1000
+    for k in ("keys", "point_list", "ranges", "n_contrib", "color", "alpha"):
+        assert np.array_equal(a[k], b[k]), k
+
+
+def test_non_contiguous_and_sentinel_inputs():
+    sc = U.make_scene(P=800, W=48, H=48, seed=24)
+    base, _ = _call(sc, requires_grad=False)
+    t = U.to_torch(sc)
+    wide = torch.zeros(800, 6, device="cuda")
+    wide[:, ::2] = t["means3D"]
+    out, _ = _call(sc, requires_grad=False, means3D=wide[:, ::2])
+    for a, b in zip(base, out):
+        assert torch.equal(a, b)
+
+
+def test_mark_visible():
+    from diff_gauss import GaussianRasterizer
+    sc = U.make_scene(P=4000, W=32, H=32, seed=3, extent=0.8)
+    t = U.to_torch(sc)
+    vis = GaussianRasterizer(U.settings_from(t)).markVisible(t["means3D"])
+    from oracle import cpu_oracle as O
+    assert vis.dtype == torch.bool
+    assert np.array_equal(vis.cpu().numpy(), O.mark_visible(sc["means3D"], sc["viewmatrix"], sc["projmatrix"]))
+
+
+def test_reference_error_texts():
+    from diff_gauss import GaussianRasterizer
+    sc = U.make_scene(P=10, W=16, H=16, seed=3)
+    t = U.to_torch(sc)
+    r = GaussianRasterizer(U.settings_from(t))
+    m2 = torch.zeros_like(t["means3D"])
+    with pytest.raises(Exception, match="excatly one of either SHs or precomputed colors"):
+        r(means3D=t["means3D"], means2D=m2, opacities=t["opacities"], scales=t["scales"], rotations=t["rotations"])
+    with pytest.raises(Exception, match="exactly one of either scale/rotation pair"):
+        r(means3D=t["means3D"], means2D=m2, opacities=t["opacities"], colors_precomp=t["colors_precomp"])
+    with pytest.raises(ValueError, match="scales == None is not allowed"):
+        r(means3D=t["means3D"], means2D=m2, opacities=t["opacities"], colors_precomp=t["colors_precomp"],
+          cov3Ds_precomp=torch.zeros(10, 6, device="cuda"))
+    with pytest.raises(RuntimeError, match="CUDA-only"):
+        r(means3D=t["means3D"].cpu(), means2D=m2, opacities=t["opacities"], colors_precomp=t["colors_precomp"],
+          scales=t["scales"], rotations=t["rotations"])

@@ -107,3 +107,130 @@ def bin_capacity_from_bytes(nbytes):
     while cap > 1 and lib.igs_bin_bytes(cap - 1) >= nbytes:
         cap -= 1
     return cap
+
+
+# ---------------------------------------------------------------------------
+# running the three implementations on one scene
+# ---------------------------------------------------------------------------
+GRAD_NAMES = ("dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dnorm3D", "dL_dsh",
+              "dL_dscales", "dL_drotations", "dL_dextra")
+
+
+def _bwd_args(tsc, rad, tg, geom, n, binb, img, alpha, debug=False):
+    import torch
+    e = torch.Tensor([])
+    ex = tsc["extra_attrs"] if tsc.get("extra_attrs") is not None else e
+    return (tsc["bg"], tsc["means3D"], rad, tsc["colors_precomp"] if tsc["colors_precomp"] is not None else e,
+            tsc["scales"], tsc["rotations"], ex, tsc.get("scale_modifier", 1.0),
+            tsc["cov3Ds_precomp"] if tsc.get("cov3Ds_precomp") is not None else e,
+            tsc["norm3Ds_precomp"] if tsc.get("norm3Ds_precomp") is not None else e,
+            tsc["viewmatrix"], tsc["projmatrix"], tsc["tanfovx"], tsc["tanfovy"], tg["color"], tg["depth"], tg["norm"],
+            tg["alpha"], tg["extra"] if ex.numel() else e, tsc["shs"] if tsc["shs"] is not None else e,
+            tsc["sh_degree"], tsc["campos"], geom, n, binb, img, alpha, debug)
+
+
+def run_igs(sc, grads=None, debug=False):
+    """Product path through the C ABI (instag_b200.rasterizer._forward_native /
+    _backward_native = the ctypes calls into libigs_raster.so).  Returns numpy."""
+    import torch
+    from instag_b200 import rasterizer as R
+    tsc = to_torch(sc)
+    P, H, W = tsc["means3D"].shape[0], sc["H"], sc["W"]
+    n, color, depth, norm, alpha, radii, extra, geom, binb, img = R._forward_native(*raw_args_fwd(tsc, debug))
+    torch.cuda.synchronize()
+    out = dict(num_rendered=n, color=color, depth=depth, norm=norm, alpha=alpha, radii=radii, extra=extra)
+    if P > 0:
+        inter = igs_intermediates(P, H, W, n, geom, binb, img)
+        inter.pop("_bin")
+        cap = bin_capacity_from_bytes(binb.numel())
+        inter["keys"] = igs_sorted_keys(binb, cap, n)
+        cl = inter.pop("clamped")
+        inter["clamped"] = torch.stack([(cl >> c) & 1 for c in range(3)], dim=1)
+        out.update(inter)
+    if grads is not None:
+        tg = {k: torch.from_numpy(v).cuda() for k, v in grads.items()}
+        res = R._backward_native(*_bwd_args(tsc, radii, tg, geom, n, binb, img, alpha, debug))
+        torch.cuda.synchronize()
+        out.update(dict(zip(GRAD_NAMES, res)))
+    return {k: (v.detach().cpu().numpy() if hasattr(v, "detach") else v) for k, v in out.items()}
+
+
+def run_ref(sc, grads=None):
+    """The unmodified reference (oracle/_ref/libdgr_ref.so) on the same inputs."""
+    import torch
+    from oracle import ref_cuda as RC
+    tsc = to_torch(sc)
+    P, H, W = tsc["means3D"].shape[0], sc["H"], sc["W"]
+    n, color, depth, norm, alpha, radii, extra, geom, binb, img = RC.forward_raw(*raw_args_fwd(tsc))
+    torch.cuda.synchronize()
+    out = dict(num_rendered=n, color=color, depth=depth, norm=norm, alpha=alpha, radii=radii, extra=extra)
+    if P > 0:
+        out.update(RC.intermediates(P, H, W, n, geom, binb, img))
+    if grads is not None:
+        tg = {k: torch.from_numpy(v).cuda() for k, v in grads.items()}
+        res = RC.backward_raw(*_bwd_args(tsc, radii, tg, geom, n, binb, img, alpha))
+        torch.cuda.synchronize()
+        out.update(dict(zip(GRAD_NAMES, res)))
+    return {k: (v.detach().cpu().numpy() if hasattr(v, "detach") else v) for k, v in out.items()}
+
+
+def run_oracle(sc, grads=None):
+    """CPU restatement (oracle/), same dictionary keys."""
+    from oracle import cpu_oracle as O
+    s = oracle_scene(sc)
+    f = O.forward(s)
+    out = dict(f)
+    out["means2D"] = f["means2D"]
+    out["clamped"] = f["clamped"]
+    if grads is not None:
+        b = O.backward(s, f, grads["color"], grads["depth"], grads["norm"], grads["alpha"], grads.get("extra"))
+        out.update(b)
+    return out
+
+
+# ---------------------------------------------------------------------------
+# comparison helpers (the tolerances of BASELINE.json, written out)
+# ---------------------------------------------------------------------------
+IMG_ATOL = 1e-5    # color / depth / alpha / norm / extra: max-abs
+GRAD_RTOL = 1e-4   # gradients: max-abs error relative to the tensor's max-abs
+
+
+def rel_err(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    if a.size == 0:
+        return 0.0
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-20))
+
+
+def assert_ints_equal(a, b, names, vis=None):
+    for k in names:
+        x, y = np.asarray(a[k]), np.asarray(b[k])
+        assert x.shape == y.shape, f"{k}: shape {x.shape} vs {y.shape}"
+        assert np.array_equal(x.astype(np.int64), y.astype(np.int64)), \
+            f"{k}: {int((x.astype(np.int64) != y.astype(np.int64)).sum())} of {x.size} differ"
+
+
+def assert_forward_close(a, b, atol=IMG_ATOL, mask=None, heads=("color", "depth", "norm", "alpha", "extra")):
+    """mask: optional [H*W] bool of pixels to EXCLUDE (oracle borderline pixels)."""
+    for k in heads:
+        x, y = np.asarray(a[k]), np.asarray(b[k])
+        assert x.shape == y.shape, f"{k}: shape {x.shape} vs {y.shape}"
+        if x.size == 0:
+            continue
+        d = np.abs(x - y).reshape(x.shape[0], -1)
+        if mask is not None:
+            d = d[:, ~mask]
+        assert d.size == 0 or d.max() <= atol, f"{k}: max-abs {d.max():.3e} > {atol}"
+
+
+def assert_grads_close(a, b, rtol=GRAD_RTOL, names=GRAD_NAMES):
+    bad = []
+    for k in names:
+        if k not in a or k not in b:
+            continue
+        x, y = np.asarray(a[k]), np.asarray(b[k])
+        assert x.shape == y.shape, f"{k}: shape {x.shape} vs {y.shape}"
+        r = rel_err(x, y)
+        if not r <= rtol:
+            bad.append(f"{k}: rel {r:.3e}")
+    assert not bad, "; ".join(bad)

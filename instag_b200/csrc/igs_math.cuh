@@ -12,13 +12,13 @@ struct Rot { float m[3][3]; };
 __device__ __forceinline__ Rot quat_to_rot(float4 q) {
   const float r = q.x, x = q.y, y = q.z, z = q.w;
   Rot R;
-  R.m[0][0] = __fmaf_rn(-2.f, __fmaf_rn(y, y, __fmul_rn(z, z)), 1.f);
+  R.m[0][0] = __fsub_rn(1.f, __fmul_rn(2.f, __fadd_rn(__fmul_rn(y, y), __fmul_rn(z, z)))); // yy, zz shared: not fused
   R.m[0][1] = 2.f * __fmaf_rn(x, y, -__fmul_rn(r, z));
-  R.m[0][2] = 2.f * __fmaf_rn(x, z, __fmul_rn(r, y));
+  R.m[0][2] = 2.f * __fmaf_rn(r, y, __fmul_rn(x, z));  // x*z is the shared rounded product
   R.m[1][0] = 2.f * __fmaf_rn(x, y, __fmul_rn(r, z));
   R.m[1][1] = __fmaf_rn(-2.f, __fmaf_rn(x, x, __fmul_rn(z, z)), 1.f);
   R.m[1][2] = 2.f * __fmaf_rn(y, z, -__fmul_rn(r, x));
-  R.m[2][0] = 2.f * __fmaf_rn(x, z, -__fmul_rn(r, y));
+  R.m[2][0] = 2.f * __fmaf_rn(-r, y, __fmul_rn(x, z));
   R.m[2][1] = 2.f * __fmaf_rn(y, z, __fmul_rn(r, x));
   R.m[2][2] = __fmaf_rn(-2.f, __fmaf_rn(x, x, __fmul_rn(y, y)), 1.f);
   return R;

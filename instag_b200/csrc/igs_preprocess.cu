@@ -29,7 +29,7 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float* __restrict__ s
 #define SHK(k) __ldg(sh + 3 * (k) + c)
     float r = __fmul_rn(kSH_C0, SHK(0));
     if (deg > 0) {
-      r = __fmaf_rn(kSH_C0, SHK(0), -__fmul_rn(__fmul_rn(kSH_C1, y), SHK(1)));
+      r = __fmaf_rn(-__fmul_rn(kSH_C1, y), SHK(1), r); // the degree-0 product stays rounded
       r = __fmaf_rn(__fmul_rn(kSH_C1, z), SHK(2), r);
       r = __fmaf_rn(-__fmul_rn(kSH_C1, x), SHK(3), r);
       if (deg > 1) {
@@ -37,18 +37,18 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float* __restrict__ s
         const float xy = __fmul_rn(x, y), yz = __fmul_rn(y, z), xz = __fmul_rn(x, z);
         r = __fmaf_rn(__fmul_rn(kSH_C2[0], xy), SHK(4), r);
         r = __fmaf_rn(__fmul_rn(kSH_C2[1], yz), SHK(5), r);
-        r = __fmaf_rn(__fmul_rn(kSH_C2[2], __fmaf_rn(-y, y, __fmaf_rn(2.f, zz, -xx))), SHK(6), r);
+        r = __fmaf_rn(__fmul_rn(kSH_C2[2], __fsub_rn(__fmaf_rn(2.f, zz, -xx), yy)), SHK(6), r);
         r = __fmaf_rn(__fmul_rn(kSH_C2[3], xz), SHK(7), r);
-        r = __fmaf_rn(__fmul_rn(kSH_C2[4], __fmaf_rn(x, x, -yy)), SHK(8), r);
+        r = __fmaf_rn(__fmul_rn(kSH_C2[4], __fsub_rn(xx, yy)), SHK(8), r);
         if (deg > 2) {
           r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[0], y), __fmaf_rn(3.f, xx, -yy)), SHK(9), r);
           r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[1], xy), z), SHK(10), r);
-          r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[2], y), __fmaf_rn(-y, y, __fmaf_rn(4.f, zz, -xx))), SHK(11), r);
+          r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[2], y), __fsub_rn(__fmaf_rn(4.f, zz, -xx), yy)), SHK(11), r);
           r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[3], z),
-                                  __fmaf_rn(-3.f, yy, __fmaf_rn(2.f, zz, -__fmul_rn(3.f, xx)))), SHK(12), r);
-          r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[4], x), __fmaf_rn(-y, y, __fmaf_rn(4.f, zz, -xx))), SHK(13), r);
-          r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[5], z), __fmaf_rn(x, x, -yy)), SHK(14), r);
-          r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[6], x), __fmaf_rn(x, x, -__fmul_rn(3.f, yy))), SHK(15), r);
+                                  __fmaf_rn(-3.f, yy, __fmaf_rn(-3.f, xx, __fmul_rn(2.f, zz)))), SHK(12), r);
+          r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[4], x), __fsub_rn(__fmaf_rn(4.f, zz, -xx), yy)), SHK(13), r);
+          r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[5], z), __fsub_rn(xx, yy)), SHK(14), r);
+          r = __fmaf_rn(__fmul_rn(__fmul_rn(kSH_C3[6], x), __fmaf_rn(-3.f, yy, xx)), SHK(15), r);
         }
       }
     }

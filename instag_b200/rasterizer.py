@@ -167,11 +167,13 @@ def _backward_native(bg, means3D, radii, colors_precomp, scales, rotations, extr
     sc = _get_scratch(dev)
     # one allocation for all per-Gaussian gradients, contiguous sub-blocks
     widths = [3, 3, 1, 3, 6, 3, 3 * M, 3, 4, ED]
-    flat = torch.empty((P * sum(widths),), dtype=torch.float32, device=dev)
-    outs, o = [], 0
+    # (every block starts 16-byte aligned, as the C ABI requires)
+    starts, o = [], 0
     for w in widths:
-        outs.append(flat[o:o + P * w].view(P, w))
-        o += P * w
+        starts.append(o)
+        o += (P * w + 3) // 4 * 4
+    flat = torch.empty((o,), dtype=torch.float32, device=dev)
+    outs = [flat[st:st + P * w].view(P, w) for st, w in zip(starts, widths)]
     (g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_norm3D, g_sh, g_scales, g_rot, g_extra) = outs
     g_sh = g_sh.view(P, M, 3)
     if ED == 0:

@@ -12,13 +12,13 @@ static void build_R(const float* q, m3* R)
 {
   float r = q[0], x = q[1], y = q[2], z = q[3];
   /* glm::mat3(a,b,c, d,e,f, g,h,i) fills COLUMNS: R->m[0] = (a,b,c) ... */
-  R->m[0][0] = fmaf(-2.f, fmaf(y, y, z * z), 1.f);
+  R->m[0][0] = 1.f - 2.f * (y * y + z * z);           /* SASS: FADD(yy,zz): both products are shared, none fused */
   R->m[0][1] = 2.f * fmaf(x, y, -(r * z));
-  R->m[0][2] = 2.f * fmaf(x, z, r * y);
+  R->m[0][2] = 2.f * fmaf(r, y, x * z);               /* SASS: x*z is the shared rounded product */
   R->m[1][0] = 2.f * fmaf(x, y, r * z);
   R->m[1][1] = fmaf(-2.f, fmaf(x, x, z * z), 1.f);
   R->m[1][2] = 2.f * fmaf(y, z, -(r * x));
-  R->m[2][0] = 2.f * fmaf(x, z, -(r * y));
+  R->m[2][0] = 2.f * fmaf(-r, y, x * z);
   R->m[2][1] = 2.f * fmaf(y, z, r * x);
   R->m[2][2] = fmaf(-2.f, fmaf(x, x, y * y), 1.f);
 }
@@ -110,24 +110,24 @@ static void color_from_sh(int idx, int deg, int M, const float* means, const flo
     if (deg > 0) {
       /* result - C1*y*sh1 + C1*z*sh2 - C1*x*sh3 ; the first product is the
        * left operand of the first subtraction and is the one fused. */
-      res = fmaf(SH_C0, SH(0), -((SH_C1 * y) * SH(1)));
+      res = fmaf(-(SH_C1 * y), SH(1), SH_C0 * SH(0)); /* SASS: the degree-0 product is rounded, this one fused */
       res = fmaf(SH_C1 * z, SH(2), res);
       res = fmaf(-(SH_C1 * x), SH(3), res);
       if (deg > 1) {
         float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
         res = fmaf(SH_C2[0] * xy, SH(4), res);
         res = fmaf(SH_C2[1] * yz, SH(5), res);
-        res = fmaf(SH_C2[2] * fmaf(-y, y, fmaf(2.f, zz, -xx)), SH(6), res);
+        res = fmaf(SH_C2[2] * ((2.f * zz - xx) - yy), SH(6), res); /* xx, yy, zz are shared rounded products */
         res = fmaf(SH_C2[3] * xz, SH(7), res);
-        res = fmaf(SH_C2[4] * fmaf(x, x, -yy), SH(8), res);
+        res = fmaf(SH_C2[4] * (xx - yy), SH(8), res);
         if (deg > 2) {
           res = fmaf(SH_C3[0] * y * fmaf(3.f, xx, -yy), SH(9), res);
           res = fmaf(SH_C3[1] * xy * z, SH(10), res);
-          res = fmaf(SH_C3[2] * y * fmaf(-y, y, fmaf(4.f, zz, -xx)), SH(11), res);
-          res = fmaf(SH_C3[3] * z * fmaf(-3.f, yy, fmaf(2.f, zz, -(3.f * xx))), SH(12), res);
-          res = fmaf(SH_C3[4] * x * fmaf(-y, y, fmaf(4.f, zz, -xx)), SH(13), res);
-          res = fmaf(SH_C3[5] * z * fmaf(x, x, -yy), SH(14), res);
-          res = fmaf(SH_C3[6] * x * fmaf(x, x, -(3.f * yy)), SH(15), res);
+          res = fmaf(SH_C3[2] * y * (fmaf(4.f, zz, -xx) - yy), SH(11), res);
+          res = fmaf(SH_C3[3] * z * fmaf(-3.f, yy, fmaf(-3.f, xx, 2.f * zz)), SH(12), res);
+          res = fmaf(SH_C3[4] * x * (fmaf(4.f, zz, -xx) - yy), SH(13), res);
+          res = fmaf(SH_C3[5] * z * (xx - yy), SH(14), res);
+          res = fmaf(SH_C3[6] * x * fmaf(-3.f, yy, xx), SH(15), res);
         }
       }
     }

@@ -50,7 +50,8 @@ def _check_against(ours, theirs, sc, exact_geom=True, floor=0.0, border=None):
         else:
             assert np.abs(a - b).max() <= 1e-6
     if sc["shs"] is not None:
-        assert np.abs(np.asarray(ours["rgb"])[vis] - np.asarray(theirs["rgb"])[vis]).max() <= 1e-6
+        a, b = np.asarray(ours["rgb"])[vis], np.asarray(theirs["rgb"])[vis]
+        assert np.array_equal(a, b) if exact_geom else np.abs(a - b).max() <= 1e-6, "rgb"
         assert np.array_equal(np.asarray(ours["clamped"])[vis].astype(bool),
                               np.asarray(theirs["clamped"])[vis].astype(bool))
     mask = None

@@ -47,7 +47,7 @@ def test_oracle_matches_reference_golden(name):
     for k in ("means2D", "depths", "conic_opacity", "norm3D", "cov3D"):
         assert np.array_equal(np.asarray(o[k])[vis], gold[k][vis]), f"{k} not bit-exact on visible Gaussians"
     if sc["shs"] is not None:
-        assert np.abs(np.asarray(o["rgb"])[vis] - gold["rgb"][vis]).max() <= 1e-6
+        assert np.array_equal(np.asarray(o["rgb"])[vis], gold["rgb"][vis]), "rgb not bit-exact"
         assert np.array_equal(np.asarray(o["clamped"])[vis].astype(bool), gold["clamped"][vis].astype(bool))
     # pixels where an expf-dependent threshold is within a few ulp of flipping are excluded
     border = o["borderline"].astype(bool)

@@ -19,11 +19,13 @@ constexpr float T_MIN = 0.0001f;
 //  r0 = {conic.x, conic.y, conic.z, opacity}
 //  r1 = {mean2D.x, mean2D.y, view depth, extra[0]}
 //  r2 = {r, g, b, normal.x}
-//  r3 = {normal.y, normal.z, -, -}
+//  r3 = {normal.y, normal.z, cut, -}   cut = 2 ln(255 opacity): the splat can only
+//       blend (alpha >= 1/255) where  a dx^2 + 2 b dx dy + c dy^2 <= cut
 constexpr int SPLAT_F4 = 4;
 
 // ---- gradient accumulator: 16 floats = 64 B per Gaussian -------------------
-//  0,1 dL/dmean2D.xy | 2,3,4 dL/dconic.{x,y,w} | 5 dL/dopacity | 6..8 dL/dcolor
+//  with g = G * dL/dalpha summed over the pixels that blend the splat and (dx,dy) = centre - pixel:
+//  0,1 sum g dx, g dy | 2,3,4 sum g dx^2, g dx dy, g dy^2 | 5 sum g (= dL/dopacity) | 6..8 dL/dcolor
 //  9 dL/ddepth | 10..12 dL/dnormal | 13 dL/dextra[0] | 14,15 unused
 constexpr int ACC_F = 16;
 
@@ -166,6 +168,37 @@ __device__ __forceinline__ void tile_rect(float px, float py, int radius, int gx
 __device__ __forceinline__ float gauss_power(float cx, float cy, float cz, float dx, float dy) {
   const float s = __fmaf_rn(__fmul_rn(cx, dx), dx, __fmul_rn(__fmul_rn(cz, dy), dy));
   return __fmaf_rn(s, -0.5f, -__fmul_rn(__fmul_rn(cy, dx), dy));
+}
+
+// ---- warp-level culling --------------------------------------------------
+// Can the splat {conic (a,b,c), mean (mx,my), cut} blend into ANY pixel of the
+// pixel rectangle [x0,x1] x [y0,y1]?  A pixel blends only if
+//   power = -q/2 <= 0  and  opacity*exp(power) >= 1/255   <=>   q <= cut,
+// q = a dx^2 + 2 b dx dy + c dy^2.  q is convex (the conic is positive definite), so
+// its minimum over the rectangle is 0 if the mean is inside, else it lies on one of the
+// (at most two) edges facing the mean, where it is a clamped 1-D quadratic minimum.
+// CONSERVATIVE by construction: a margin covers fp32 rounding of q here and of `power`
+// in the compositing loops, every comparison is written so that NaN means "keep",
+// and a conic that is not positive definite is always kept.  Culling therefore never
+// changes a result, it only skips work (tests/test_gpu_parity.py checks n_contrib and
+// the images against the unculled reference on every scene).
+__device__ __forceinline__ bool splat_may_touch(float a, float b, float c, float mx, float my, float cut,
+                                                float x0, float x1, float y0, float y1) {
+  const float ex0 = x0 - mx, ex1 = x1 - mx, ey0 = y0 - my, ey1 = y1 - my;
+  const float dxn = fminf(fmaxf(0.f, ex0), ex1); // offset of the nearest rectangle point
+  const float dyn = fminf(fmaxf(0.f, ey0), ey1);
+  // facing vertical edge (dx = dxn): minimise over dy
+  const float dy1 = fminf(fmaxf(__fdividef(-b * dxn, c), ey0), ey1);
+  const float p1 = a * dxn * dxn, p2 = 2.f * b * dxn * dy1, p3 = c * dy1 * dy1;
+  // facing horizontal edge (dy = dyn): minimise over dx
+  const float dx2 = fminf(fmaxf(__fdividef(-b * dyn, a), ex0), ex1);
+  const float r1 = a * dx2 * dx2, r2 = 2.f * b * dx2 * dyn, r3 = c * dyn * dyn;
+  const float q1 = p1 + p2 + p3, m1 = p1 + fabsf(p2) + p3;
+  const float q2 = r1 + r2 + r3, m2 = r1 + fabsf(r2) + r3;
+  const bool far1 = q1 > cut + 0.01f + 1e-5f * m1;
+  const bool far2 = q2 > cut + 0.01f + 1e-5f * m2;
+  const bool pd = a > 0.f && c > 0.f && a * c > b * b;
+  return !(far1 && far2 && pd);
 }
 
 } // namespace igs

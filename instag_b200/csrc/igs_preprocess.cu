@@ -187,7 +187,8 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
                                __ldg(a.opacities + idx));
           rec[1] = make_float4(sx, sy, vz, e0);
           rec[2] = make_float4(rgb.x, rgb.y, rgb.z, nx);
-          rec[3] = make_float4(ny, nz, 0.f, 0.f);
+          const float op = __ldg(a.opacities + idx);
+          rec[3] = make_float4(ny, nz, 2.f * logf(255.f * op), 0.f); // culling bound, see splat_may_touch
         }
       }
     }

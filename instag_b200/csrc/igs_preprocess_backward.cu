@@ -104,7 +104,25 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(BwdPreArgs a) 
   const float* proj = s_proj;
 
   const float4* acc = reinterpret_cast<const float4*>(a.accum) + (size_t)idx * (ACC_F / 4);
-  const float4 g0 = __ldg(acc), g1 = __ldg(acc + 1), g2 = __ldg(acc + 2), g3 = __ldg(acc + 3);
+  float4 g0 = __ldg(acc), g1 = __ldg(acc + 1);
+  const float4 g2 = __ldg(acc + 2), g3 = __ldg(acc + 3);
+  const bool visible = __ldg(a.radii + idx) > 0;
+  // The compositing backward leaves raw moments of g = G*dL/dalpha about the splat centre
+  // (igs_common.cuh ACC_F); with dL/dG = opacity * dL/dalpha (reference backward.cu:690-709):
+  //   dL/dmean2D.x = -0.5 W o (a Sx + b Sy)   dL/dmean2D.y = -0.5 H o (c Sy + b Sx)
+  //   dL/dconic.{x,y,w} = -0.5 o {Sxx, Sxy, Syy}      dL/dopacity = S
+  if (visible) {
+    const float4 co = __ldg(a.splat + (size_t)idx * SPLAT_F4); // conic.xyz, opacity
+    const float Sx = g0.x, Sy = g0.y, Sxx = g0.z, Sxy = g0.w, Syy = g1.x;
+    g0.x = -0.5f * a.W * co.w * (co.x * Sx + co.y * Sy);
+    g0.y = -0.5f * a.H * co.w * (co.z * Sy + co.y * Sx);
+    g0.z = -0.5f * co.w * Sxx;
+    g0.w = -0.5f * co.w * Sxy;
+    g1.x = -0.5f * co.w * Syy;
+  } else {
+    g0 = make_float4(0.f, 0.f, 0.f, 0.f);
+    g1.x = 0.f;
+  }
   // g0 = (m2d.x, m2d.y, conic.x, conic.y) g1 = (conic.w, opacity, col.r, col.g)
   // g2 = (col.b, depth, n.x, n.y)         g3 = (n.z, extra0, -, -)
   a.dL_dmeans2D[3 * idx] = g0.x; a.dL_dmeans2D[3 * idx + 1] = g0.y; a.dL_dmeans2D[3 * idx + 2] = 0.f;
@@ -121,7 +139,7 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(BwdPreArgs a) 
   float4 drot = make_float4(0.f, 0.f, 0.f, 0.f);
   float* dsh = USE_SH ? a.dL_dsh + (size_t)idx * a.M * 3 : nullptr;
 
-  if (__ldg(a.radii + idx) > 0) {
+  if (visible) {
     const float mx = __ldg(a.means3D + 3 * idx), my = __ldg(a.means3D + 3 * idx + 1), mz = __ldg(a.means3D + 3 * idx + 2);
     const float3 sc = make_float3(__ldg(a.scales + 3 * idx), __ldg(a.scales + 3 * idx + 1), __ldg(a.scales + 3 * idx + 2));
     const float4 q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);

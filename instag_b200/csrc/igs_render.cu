@@ -32,15 +32,18 @@ __global__ void __launch_bounds__(TILE_PIX) render_kernel(RenderArgs a) {
   __shared__ float4 s_r0[BATCH]; // conic.xyz, opacity
   __shared__ float4 s_r1[BATCH]; // x, y, depth, extra0
   __shared__ float4 s_r2[BATCH]; // r, g, b, nx
-  __shared__ float2 s_r3[BATCH]; // ny, nz
+  __shared__ float4 s_r3[BATCH]; // ny, nz, cut, -
   __shared__ uint32_t s_id[ED_T < 0 ? BATCH : 1];
 
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   int lx, ly;
   thread_pixel(tid, lx, ly);
   const int px = blockIdx.x * TILE + lx, py = blockIdx.y * TILE + ly;
   const bool inside = px < a.W && py < a.H;
   const float pxf = (float)px, pyf = (float)py;
+  // the 8x4 pixel rectangle of this warp (culling)
+  const float wx0 = (float)(blockIdx.x * TILE + (warp & 1) * 8), wx1 = wx0 + 7.f;
+  const float wy0 = (float)(blockIdx.y * TILE + (warp >> 1) * 4), wy1 = wy0 + 3.f;
   const uint2 range = a.ranges[blockIdx.y * a.grid_x + blockIdx.x];
   const int total = (int)(range.y - range.x);
   const int ED = ED_T < 0 ? a.ED : ED_T;
@@ -65,39 +68,52 @@ __global__ void __launch_bounds__(TILE_PIX) render_kernel(RenderArgs a) {
       s_r0[tid] = __ldg(rec);
       s_r1[tid] = __ldg(rec + 1);
       s_r2[tid] = __ldg(rec + 2);
-      const float4 r3 = __ldg(rec + 3);
-      s_r3[tid] = make_float2(r3.x, r3.y);
+      s_r3[tid] = __ldg(rec + 3);
       if (ED_T < 0) s_id[tid] = id;
     }
     __syncthreads();
-    if (__all_sync(0xffffffffu, done)) continue; // warp-level early termination
-    for (int j = 0; j < n && !done; j++) {
-      const float4 r1 = s_r1[j];
-      const float4 r0 = s_r0[j];
-      const float dx = __fsub_rn(r1.x, pxf), dy = __fsub_rn(r1.y, pyf);
-      const float power = gauss_power(r0.x, r0.y, r0.z, dx, dy);
-      if (power > 0.0f) continue;
-      const float alpha = fminf(0.99f, __fmul_rn(r0.w, expf(power)));
-      if (alpha < ALPHA_MIN) continue;
-      const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
-      if (test_T < T_MIN) { done = true; continue; }
-      // X += f*alpha*T  ->  fma(f*alpha, T, X)   (reference forward.cu:425-431)
-      const float4 r2 = s_r2[j];
-      const float2 r3 = s_r3[j];
-      C0 = __fmaf_rn(__fmul_rn(r2.x, alpha), T, C0);
-      C1 = __fmaf_rn(__fmul_rn(r2.y, alpha), T, C1);
-      C2 = __fmaf_rn(__fmul_rn(r2.z, alpha), T, C2);
-      Dp = __fmaf_rn(__fmul_rn(r1.z, alpha), T, Dp);
-      N0 = __fmaf_rn(__fmul_rn(r2.w, alpha), T, N0);
-      N1 = __fmaf_rn(__fmul_rn(r3.x, alpha), T, N1);
-      N2 = __fmaf_rn(__fmul_rn(r3.y, alpha), T, N2);
-      if (ED_T == 1) E0 = __fmaf_rn(__fmul_rn(r1.w, alpha), T, E0);
-      if (ED_T < 0) {
-        const float* e = a.extra_attrs + (size_t)s_id[j] * ED;
-        for (int c = 0; c < ED; c++) Ex[c] = __fmaf_rn(__fmul_rn(__ldg(e + c), alpha), T, Ex[c]);
+    // warp-level early termination + warp-level culling: 32 splats at a time, each lane
+    // tests one against the warp's pixel rectangle; only survivors are composited
+    for (int cb = 0; cb < n; cb += 32) {
+      if (__all_sync(0xffffffffu, done)) break;
+      bool hit = false;
+      if (cb + lane < n) {
+        const float4 q0 = s_r0[cb + lane];
+        const float4 q1 = s_r1[cb + lane];
+        hit = splat_may_touch(q0.x, q0.y, q0.z, q1.x, q1.y, s_r3[cb + lane].z, wx0, wx1, wy0, wy1);
       }
-      T = test_T;
-      last_contributor = (uint32_t)(base + j + 1);
+      unsigned m = __ballot_sync(0xffffffffu, hit);
+      while (m) {
+        const int j = cb + __ffs(m) - 1;
+        m &= m - 1;
+        if (done) continue;
+        const float4 r1 = s_r1[j];
+        const float4 r0 = s_r0[j];
+        const float dx = __fsub_rn(r1.x, pxf), dy = __fsub_rn(r1.y, pyf);
+        const float power = gauss_power(r0.x, r0.y, r0.z, dx, dy);
+        if (power > 0.0f) continue;
+        const float alpha = fminf(0.99f, __fmul_rn(r0.w, expf(power)));
+        if (alpha < ALPHA_MIN) continue;
+        const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
+        if (test_T < T_MIN) { done = true; continue; }
+        // X += f*alpha*T  ->  fma(f*alpha, T, X)   (reference forward.cu:425-431)
+        const float4 r2 = s_r2[j];
+        const float4 r3 = s_r3[j];
+        C0 = __fmaf_rn(__fmul_rn(r2.x, alpha), T, C0);
+        C1 = __fmaf_rn(__fmul_rn(r2.y, alpha), T, C1);
+        C2 = __fmaf_rn(__fmul_rn(r2.z, alpha), T, C2);
+        Dp = __fmaf_rn(__fmul_rn(r1.z, alpha), T, Dp);
+        N0 = __fmaf_rn(__fmul_rn(r2.w, alpha), T, N0);
+        N1 = __fmaf_rn(__fmul_rn(r3.x, alpha), T, N1);
+        N2 = __fmaf_rn(__fmul_rn(r3.y, alpha), T, N2);
+        if (ED_T == 1) E0 = __fmaf_rn(__fmul_rn(r1.w, alpha), T, E0);
+        if (ED_T < 0) {
+          const float* e = a.extra_attrs + (size_t)s_id[j] * ED;
+          for (int c = 0; c < ED; c++) Ex[c] = __fmaf_rn(__fmul_rn(__ldg(e + c), alpha), T, Ex[c]);
+        }
+        T = test_T;
+        last_contributor = (uint32_t)(base + j + 1);
+      }
     }
   }
 

@@ -11,6 +11,9 @@
 // ballot; the tail of the list behind every pixel's last contributor is skipped
 // without being loaded.
 //
+// Each warp first culls the staged splats against its own 8x4 pixel rectangle
+// (splat_may_touch, igs_common.cuh), 32 at a time, and only walks the survivors.
+//
 // Bound: FP32 issue + L2 atomics.  Per blended pair ~110 flop.
 #include "igs_common.cuh"
 #include "igs_kernels.cuh"
@@ -55,16 +58,18 @@ __global__ void __launch_bounds__(TILE_PIX) render_backward_kernel(BwdRenderArgs
   __shared__ float4 s_r0[BATCH];
   __shared__ float4 s_r1[BATCH];
   __shared__ float4 s_r2[BATCH];
-  __shared__ float2 s_r3[BATCH];
+  __shared__ float4 s_r3[BATCH];
   __shared__ uint32_t s_id[BATCH];
   __shared__ uint32_t s_max_contrib;
 
-  const int tid = threadIdx.x, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   int lx, ly;
   thread_pixel_b(tid, lx, ly);
   const int px = blockIdx.x * TILE + lx, py = blockIdx.y * TILE + ly;
   const bool inside = px < a.W && py < a.H;
   const float pxf = (float)px, pyf = (float)py;
+  const float wx0 = (float)(blockIdx.x * TILE + (warp & 1) * 8), wx1 = wx0 + 7.f;
+  const float wy0 = (float)(blockIdx.y * TILE + (warp >> 1) * 4), wy1 = wy0 + 3.f;
   const size_t HW = (size_t)a.H * a.W, pix = (size_t)py * a.W + px;
   const uint2 range = a.ranges[blockIdx.y * a.grid_x + blockIdx.x];
   const int total = (int)(range.y - range.x);
@@ -82,15 +87,12 @@ __global__ void __launch_bounds__(TILE_PIX) render_backward_kernel(BwdRenderArgs
     dpa = a.dL_dalpha[pix];
     if (ED >= 1) dpe0 = a.dL_dextra[pix];
   }
-  float ac0 = 0, ac1 = 0, ac2 = 0, ad = 0, an0 = 0, an1 = 0, an2 = 0, aa = 0, ae0 = 0; // accum_re*
-  float lc0 = 0, lc1 = 0, lc2 = 0, ld = 0, ln0 = 0, ln1 = 0, ln2 = 0, le0 = 0, last_alpha = 0; // last_*
-  float ax[ED_T < 0 ? IGS_MAX_EXTRA_DIMS : 1], lxe[ED_T < 0 ? IGS_MAX_EXTRA_DIMS : 1];
-  if (ED_T < 0) {
-#pragma unroll
-    for (int c = 0; c < IGS_MAX_EXTRA_DIMS; c++) { ax[c] = 0.f; lxe[c] = 0.f; }
-  }
+  // The reference keeps one running "colour behind me" per channel (accum_rec*, last_*,
+  // backward.cu:640-675) and sums (c - accum)*dL_dpixel over the channels.  Both are linear,
+  // so ONE scalar recurrence on  u = <attributes, dL_dpixel> + dL_dalpha_pixel  gives the same sum:
+  //   A <- last_alpha*u_last + (1-last_alpha)*A ;  dL_dalpha = (u - A)*T + background term.
+  float A = 0.f, u_last = 0.f, last_alpha = 0.f;
   const float bg_dot = __ldg(a.bg) * dpc0 + __ldg(a.bg + 1) * dpc1 + __ldg(a.bg + 2) * dpc2;
-  const float ddelx_dx = 0.5f * a.W, ddely_dy = 0.5f * a.H;
 
   // nothing behind the last contributor of ANY pixel of the tile matters
   if (tid == 0) s_max_contrib = 0;
@@ -111,77 +113,76 @@ __global__ void __launch_bounds__(TILE_PIX) render_backward_kernel(BwdRenderArgs
       s_r0[tid] = __ldg(rec);
       s_r1[tid] = __ldg(rec + 1);
       s_r2[tid] = __ldg(rec + 2);
-      const float4 r3 = __ldg(rec + 3);
-      s_r3[tid] = make_float2(r3.x, r3.y);
+      s_r3[tid] = __ldg(rec + 3);
     }
     __syncthreads();
     // first j this warp cares about: contributor = total - (rbase+j) - 1 < warp_max
     const int j0 = max(0, total - rbase - warp_max);
-    for (int j = j0; j < n; j++) {
-      const int contributor = total - (rbase + j) - 1;
-      const float4 r1 = s_r1[j];
-      const float4 r0 = s_r0[j];
-      const float dx = __fsub_rn(r1.x, pxf), dy = __fsub_rn(r1.y, pyf);
-      const float power = gauss_power(r0.x, r0.y, r0.z, dx, dy);
-      const float G = expf(power);
-      const float alpha = fminf(0.99f, __fmul_rn(r0.w, G));
-      const bool valid = contributor < last_contributor && !(power > 0.0f) && !(alpha < ALPHA_MIN);
-      if (!__any_sync(0xffffffffu, valid)) continue;
-      float v[16];
-#pragma unroll
-      for (int k = 0; k < 16; k++) v[k] = 0.f;
-      float weight = 0.f;
-      if (valid) {
-        const float4 r2 = s_r2[j];
-        const float2 r3 = s_r3[j];
-        T = __fdiv_rn(T, __fsub_rn(1.f, alpha));
-        weight = alpha * T;
-        const float om = 1.f - last_alpha;
-        float dL_dalpha = 0.f;
-        ac0 = last_alpha * lc0 + om * ac0; lc0 = r2.x; dL_dalpha += (r2.x - ac0) * dpc0; v[6] = weight * dpc0;
-        ac1 = last_alpha * lc1 + om * ac1; lc1 = r2.y; dL_dalpha += (r2.y - ac1) * dpc1; v[7] = weight * dpc1;
-        ac2 = last_alpha * lc2 + om * ac2; lc2 = r2.z; dL_dalpha += (r2.z - ac2) * dpc2; v[8] = weight * dpc2;
-        ad = last_alpha * ld + om * ad; ld = r1.z; dL_dalpha += (r1.z - ad) * dpd; v[9] = weight * dpd;
-        an0 = last_alpha * ln0 + om * an0; ln0 = r2.w; dL_dalpha += (r2.w - an0) * dpn0; v[10] = weight * dpn0;
-        an1 = last_alpha * ln1 + om * an1; ln1 = r3.x; dL_dalpha += (r3.x - an1) * dpn1; v[11] = weight * dpn1;
-        an2 = last_alpha * ln2 + om * an2; ln2 = r3.y; dL_dalpha += (r3.y - an2) * dpn2; v[12] = weight * dpn2;
-        if (ED >= 1) {
-          ae0 = last_alpha * le0 + om * ae0; le0 = r1.w; dL_dalpha += (r1.w - ae0) * dpe0; v[13] = weight * dpe0;
-        }
-        if (ED_T < 0) {
-          const float* e = a.extra_attrs + (size_t)s_id[j] * ED;
-          for (int c = 1; c < ED; c++) {
-            const float ev = __ldg(e + c);
-            ax[c] = last_alpha * lxe[c] + om * ax[c]; lxe[c] = ev;
-            dL_dalpha += (ev - ax[c]) * a.dL_dextra[c * HW + pix];
-          }
-        }
-        aa = last_alpha + om * aa;                    // reference backward.cu:674-675
-        dL_dalpha += (1.f - aa) * dpa;
-        dL_dalpha *= T;
-        last_alpha = alpha;
-        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot; // reference backward.cu:684-687
-        const float dL_dG = r0.w * dL_dalpha;
-        const float gdx = G * dx, gdy = G * dy;
-        const float dG_ddelx = -gdx * r0.x - gdy * r0.y;
-        const float dG_ddely = -gdy * r0.z - gdx * r0.y;
-        v[0] = dL_dG * dG_ddelx * ddelx_dx;
-        v[1] = dL_dG * dG_ddely * ddely_dy;
-        v[2] = -0.5f * gdx * dx * dL_dG;
-        v[3] = -0.5f * gdx * dy * dL_dG;
-        v[4] = -0.5f * gdy * dy * dL_dG;
-        v[5] = G * dL_dalpha;
+    for (int cb = j0 & ~31; cb < n; cb += 32) {
+      bool hit = false;
+      const int jl = cb + lane;
+      if (jl >= j0 && jl < n) {
+        const float4 q0 = s_r0[jl];
+        const float4 q1 = s_r1[jl];
+        hit = splat_may_touch(q0.x, q0.y, q0.z, q1.x, q1.y, s_r3[jl].z, wx0, wx1, wy0, wy1);
       }
-      const float tot = warp_transpose_reduce16(v, lane);
-      const uint32_t id = s_id[j];
-      const int k = lane >> 1;
-      if (!(lane & 1) && k < 13 + (ED >= 1 ? 1 : 0)) atomicAdd(a.accum + (size_t)id * ACC_F + k, tot);
-      if (ED_T < 0) { // channels 1.. : plain warp reduction into the side array
-        for (int c = 1; c < ED; c++) {
-          float gsum = valid ? weight * a.dL_dextra[c * HW + pix] : 0.f;
+      unsigned m = __ballot_sync(0xffffffffu, hit);
+      while (m) {
+        const int j = cb + __ffs(m) - 1;
+        m &= m - 1;
+        const int contributor = total - (rbase + j) - 1;
+        const float4 r1 = s_r1[j];
+        const float4 r0 = s_r0[j];
+        const float dx = __fsub_rn(r1.x, pxf), dy = __fsub_rn(r1.y, pyf);
+        const float power = gauss_power(r0.x, r0.y, r0.z, dx, dy);
+        const float G = expf(power);
+        const float alpha = fminf(0.99f, __fmul_rn(r0.w, G));
+        const bool valid = contributor < last_contributor && !(power > 0.0f) && !(alpha < ALPHA_MIN);
+        if (!__any_sync(0xffffffffu, valid)) continue;
+        // per-pixel partials; lanes that do not blend this splat contribute exact zeros
+        float weight = 0.f, gp = 0.f; // alpha*T ; G * dL/dalpha
+        if (valid) {
+          const float4 r2 = s_r2[j];
+          const float4 r3 = s_r3[j];
+          const float rc = __frcp_rn(__fsub_rn(1.f, alpha));
+          T = T * rc;                                   // reference backward.cu:612 (T / (1 - alpha))
+          weight = alpha * T;
+          float u = dpa;
+          u = fmaf(r2.x, dpc0, u); u = fmaf(r2.y, dpc1, u); u = fmaf(r2.z, dpc2, u);
+          u = fmaf(r1.z, dpd, u);
+          u = fmaf(r2.w, dpn0, u); u = fmaf(r3.x, dpn1, u); u = fmaf(r3.y, dpn2, u);
+          if (ED >= 1) u = fmaf(r1.w, dpe0, u);
+          if (ED_T < 0) {
+            const float* e = a.extra_attrs + (size_t)s_id[j] * ED;
+            for (int c = 1; c < ED; c++) u = fmaf(__ldg(e + c), a.dL_dextra[c * HW + pix], u);
+          }
+          A = fmaf(last_alpha, u_last - A, A);
+          u_last = u;
+          last_alpha = alpha;
+          // + background term, reference backward.cu:684-687
+          const float dL_dalpha = fmaf(u - A, T, -T_final * rc * bg_dot);
+          gp = G * dL_dalpha;
+        }
+        // moments of gp about the splat centre: the per-Gaussian kernel turns them into
+        // dL/dmean2D, dL/dconic and dL/dopacity (they only differ by per-Gaussian factors)
+        float v[16];
+        const float gx = gp * dx, gy = gp * dy;
+        v[0] = gx; v[1] = gy; v[2] = gx * dx; v[3] = gx * dy; v[4] = gy * dy; v[5] = gp;
+        v[6] = weight * dpc0; v[7] = weight * dpc1; v[8] = weight * dpc2; v[9] = weight * dpd;
+        v[10] = weight * dpn0; v[11] = weight * dpn1; v[12] = weight * dpn2;
+        v[13] = ED >= 1 ? weight * dpe0 : 0.f;
+        v[14] = 0.f; v[15] = 0.f;
+        const float tot = warp_transpose_reduce16(v, lane);
+        const uint32_t id = s_id[j];
+        const int k = lane >> 1;
+        if (!(lane & 1) && k < 13 + (ED >= 1 ? 1 : 0)) atomicAdd(a.accum + (size_t)id * ACC_F + k, tot);
+        if (ED_T < 0) { // channels 1.. : plain warp reduction into the side array
+          for (int c = 1; c < ED; c++) {
+            float gsum = valid ? weight * a.dL_dextra[c * HW + pix] : 0.f;
 #pragma unroll
-          for (int o = 16; o > 0; o >>= 1) gsum += __shfl_xor_sync(0xffffffffu, gsum, o);
-          if (lane == 0) atomicAdd(a.accum_extra + (size_t)id * (ED - 1) + (c - 1), gsum);
+            for (int o = 16; o > 0; o >>= 1) gsum += __shfl_xor_sync(0xffffffffu, gsum, o);
+            if (lane == 0) atomicAdd(a.accum_extra + (size_t)id * (ED - 1) + (c - 1), gsum);
+          }
         }
       }
     }

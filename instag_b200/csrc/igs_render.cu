@@ -1,15 +1,25 @@
-// Stage 4 of the forward path: per-tile front-to-back alpha compositing
+// Stage 4 of the forward path: front-to-back alpha compositing
 // (reference renderCUDA, forward.cu:321-456).
 //
-// One CTA per 16x16 tile, one thread per pixel.  Differences from the
-// reference, none of which changes a pixel's value:
-//  * each 64-byte splat record is gathered ONCE per tile into shared memory
-//    (the reference re-fetches colour/normal/depth/extra from global memory for
-//    every accepted pixel-Gaussian pair, forward.cu:426-431);
-//  * a warp covers an 8x4 pixel block (not 16x2) and leaves the batch loop as
-//    soon as its 32 pixels are done (warp-level early termination; the
-//    reference only votes per CTA, forward.cu:380);
-//  * ED (extra channels) is a template parameter: no runtime-indexed arrays.
+// The reference runs one 256-thread CTA per 16x16 tile, stages 256 splats at a
+// time behind two __syncthreads and lets every pixel walk the whole tile list.
+// Here the unit of work is ONE WARP = one 8x4 pixel block of a tile, fully
+// autonomous (no CTA barrier anywhere):
+//  * the warp walks its tile's depth-sorted list 32 entries at a time; lane l
+//    fetches entry l's {conic, opacity | x, y, depth, extra0} (32 B) and tests it
+//    against the warp's pixel rectangle (splat_may_touch, igs_common.cuh) --
+//    on the BASELINE frame 2/3 of the entries are dropped here;
+//  * survivors fetch the other 32 B of their record and park all 64 B in the
+//    warp's private shared-memory slots; the 32 pixels then composite only the
+//    survivors, reading them with broadcast LDS.128, two splats per trip so the
+//    two exp/alpha chains overlap;
+//  * ids are prefetched two chunks ahead and the cull data one chunk ahead, so
+//    the list walk never waits for an id -> record pointer chase;
+//  * a warp stops as soon as its 32 pixels are saturated (the reference only
+//    votes per CTA, forward.cu:380), and 2-warp CTAs (4096 of them at 512^2)
+//    let the hardware scheduler balance the SMs at 1/8-tile granularity.
+// None of this changes a pixel: the per-pixel arithmetic below is the
+// reference's, with the same FMA contraction (igs_common.cuh gauss_power).
 //
 // Bound: FP32 issue.  Per evaluated pair ~15 flop + 1 MUFU.EX2, per blended
 // pair +17 flop.  DRAM floor: 64 B per instance + 40 B per pixel.
@@ -18,35 +28,40 @@
 
 namespace igs {
 
-constexpr int BATCH = TILE_PIX; // Gaussians staged per round
+constexpr int RW = 2;           // warps (8x4 pixel blocks) per CTA
+constexpr int RT = RW * 32;     // threads per CTA
 
-// pixel owned by a thread: warp w covers the 8x4 block (w&1, w>>1)
-__device__ __forceinline__ void thread_pixel(int tid, int& lx, int& ly) {
-  const int w = tid >> 5, l = tid & 31;
-  lx = (w & 1) * 8 + (l & 7);
-  ly = (w >> 1) * 4 + (l >> 3);
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, float4 v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
 template <int ED_T> // 0, 1, or -1 = generic (runtime ED up to IGS_MAX_EXTRA_DIMS)
-__global__ void __launch_bounds__(TILE_PIX) render_kernel(RenderArgs a) {
-  __shared__ float4 s_r0[BATCH]; // conic.xyz, opacity
-  __shared__ float4 s_r1[BATCH]; // x, y, depth, extra0
-  __shared__ float4 s_r2[BATCH]; // r, g, b, nx
-  __shared__ float4 s_r3[BATCH]; // ny, nz, cut, -
-  __shared__ uint32_t s_id[ED_T < 0 ? BATCH : 1];
+__global__ void __launch_bounds__(RT) render_kernel(RenderArgs a) {
+  // per warp: 4 planes of 32 float4 (r0..r3 of the chunk's survivors) = 2 KB
+  __shared__ float4 s_rec[RW][4][32];
+  __shared__ uint32_t s_id[ED_T < 0 ? RW : 1][32];
 
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  int lx, ly;
-  thread_pixel(tid, lx, ly);
-  const int px = blockIdx.x * TILE + lx, py = blockIdx.y * TILE + ly;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int unit = blockIdx.x * RW + warp;          // (tile, 8x4 block)
+  const int tile = unit >> 3, wb = unit & 7;
+  if (tile >= a.grid_x * a.grid_y) return;
+  const int tx = tile % a.grid_x, ty = tile / a.grid_x;
+  const int bx = tx * TILE + (wb & 1) * 8, by = ty * TILE + (wb >> 1) * 4;
+  const int px = bx + (lane & 7), py = by + (lane >> 3);
   const bool inside = px < a.W && py < a.H;
   const float pxf = (float)px, pyf = (float)py;
-  // the 8x4 pixel rectangle of this warp (culling)
-  const float wx0 = (float)(blockIdx.x * TILE + (warp & 1) * 8), wx1 = wx0 + 7.f;
-  const float wy0 = (float)(blockIdx.y * TILE + (warp >> 1) * 4), wy1 = wy0 + 3.f;
-  const uint2 range = a.ranges[blockIdx.y * a.grid_x + blockIdx.x];
+  const float wx0 = (float)bx, wx1 = wx0 + 7.f, wy0 = (float)by, wy1 = wy0 + 3.f;
+  const uint2 range = __ldg(a.ranges + tile);
   const int total = (int)(range.y - range.x);
   const int ED = ED_T < 0 ? a.ED : ED_T;
+  const uint32_t* __restrict__ list = a.point_list + range.x;
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(&s_rec[warp][0][0]);
+  const uint32_t smine = sbase + lane * 16;         // my slot in plane 0; planes are 512 B apart
 
   float T = 1.0f;
   float C0 = 0.f, C1 = 0.f, C2 = 0.f, Dp = 0.f, N0 = 0.f, N1 = 0.f, N2 = 0.f, E0 = 0.f;
@@ -58,47 +73,73 @@ __global__ void __launch_bounds__(TILE_PIX) render_kernel(RenderArgs a) {
   uint32_t last_contributor = 0;
   bool done = !inside;
 
-  for (int base = 0; base < total; base += BATCH) {
-    // whole CTA finished?  (reference forward.cu:380)
-    if (__syncthreads_and(done)) break;
-    const int n = min(BATCH, total - base);
-    if (tid < n) {
-      const uint32_t id = __ldg(a.point_list + range.x + base + tid);
-      const float4* rec = a.splat + (size_t)id * SPLAT_F4;
-      s_r0[tid] = __ldg(rec);
-      s_r1[tid] = __ldg(rec + 1);
-      s_r2[tid] = __ldg(rec + 2);
-      s_r3[tid] = __ldg(rec + 3);
-      if (ED_T < 0) s_id[tid] = id;
+  // software pipeline: ids two chunks ahead, cull data (r0, r1) one chunk ahead
+  uint32_t id_cur = 0, id_nxt = 0;
+  float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f), q1 = q0;
+  if (lane < total) id_cur = __ldg(list + lane);
+  if (32 + lane < total) id_nxt = __ldg(list + 32 + lane);
+  if (lane < total) {
+    q0 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4);
+    q1 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4 + 1);
+  }
+
+  for (int cb = 0; cb < total; cb += 32) {
+    if (__all_sync(0xffffffffu, done)) break;
+    const bool live = cb + lane < total;
+    // cut = 2 ln(255 opacity), the record's r3.z, recomputed here so that culling needs 32 B only
+    const bool hit = live && splat_may_touch(q0.x, q0.y, q0.z, q1.x, q1.y, 2.f * __logf(255.f * q0.w),
+                                             wx0, wx1, wy0, wy1);
+    unsigned m = __ballot_sync(0xffffffffu, hit);
+    const uint32_t id_mine = id_cur;
+    const float4 c0 = q0, c1 = q1;
+    // prefetch the next chunk's cull data and the ids of the chunk after it
+    id_cur = id_nxt;
+    if (cb + 32 + lane < total) {
+      q0 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4);
+      q1 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4 + 1);
     }
-    __syncthreads();
-    // warp-level early termination + warp-level culling: 32 splats at a time, each lane
-    // tests one against the warp's pixel rectangle; only survivors are composited
-    for (int cb = 0; cb < n; cb += 32) {
-      if (__all_sync(0xffffffffu, done)) break;
-      bool hit = false;
-      if (cb + lane < n) {
-        const float4 q0 = s_r0[cb + lane];
-        const float4 q1 = s_r1[cb + lane];
-        hit = splat_may_touch(q0.x, q0.y, q0.z, q1.x, q1.y, s_r3[cb + lane].z, wx0, wx1, wy0, wy1);
-      }
-      unsigned m = __ballot_sync(0xffffffffu, hit);
-      while (m) {
-        const int j = cb + __ffs(m) - 1;
-        m &= m - 1;
-        if (done) continue;
-        const float4 r1 = s_r1[j];
-        const float4 r0 = s_r0[j];
-        const float dx = __fsub_rn(r1.x, pxf), dy = __fsub_rn(r1.y, pyf);
-        const float power = gauss_power(r0.x, r0.y, r0.z, dx, dy);
-        if (power > 0.0f) continue;
-        const float alpha = fminf(0.99f, __fmul_rn(r0.w, expf(power)));
-        if (alpha < ALPHA_MIN) continue;
+    if (cb + 64 + lane < total) id_nxt = __ldg(list + cb + 64 + lane);
+    if (m == 0) continue;
+    __syncwarp(); // everybody is done reading the previous chunk's slots
+    if (hit) {
+      const float4* rec = a.splat + (size_t)id_mine * SPLAT_F4;
+      const float4 c2 = __ldg(rec + 2), c3 = __ldg(rec + 3);
+      sts128(smine, c0);
+      sts128(smine + 512, c1);
+      sts128(smine + 1024, c2);
+      sts128(smine + 1536, c3);
+      if (ED_T < 0) s_id[warp][lane] = id_mine;
+    }
+    __syncwarp();
+    while (m) {
+      // two survivors per trip: their alpha chains are independent, only the blend is ordered
+      const int ja = __ffs(m) - 1;
+      m &= m - 1;
+      const bool two = m != 0;
+      const int jb = two ? __ffs(m) - 1 : ja;
+      m &= m - 1;
+      const float4 a1 = lds128(sbase + 512 + ja * 16), a0 = lds128(sbase + ja * 16);
+      const float4 b1 = lds128(sbase + 512 + jb * 16), b0 = lds128(sbase + jb * 16);
+      const float dxa = __fsub_rn(a1.x, pxf), dya = __fsub_rn(a1.y, pyf);
+      const float dxb = __fsub_rn(b1.x, pxf), dyb = __fsub_rn(b1.y, pyf);
+      const float pa = gauss_power(a0.x, a0.y, a0.z, dxa, dya);
+      const float pb = gauss_power(b0.x, b0.y, b0.z, dxb, dyb);
+      const float alpha_a = fminf(0.99f, __fmul_rn(a0.w, expf(pa)));
+      const float alpha_b = fminf(0.99f, __fmul_rn(b0.w, expf(pb)));
+      const bool oka = !(pa > 0.0f) && !(alpha_a < ALPHA_MIN);
+      const bool okb = two && !(pb > 0.0f) && !(alpha_b < ALPHA_MIN);
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        const bool ok = h ? okb : oka;
+        if (!ok || done) continue;
+        const float alpha = h ? alpha_b : alpha_a;
+        const int j = h ? jb : ja;
         const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
         if (test_T < T_MIN) { done = true; continue; }
         // X += f*alpha*T  ->  fma(f*alpha, T, X)   (reference forward.cu:425-431)
-        const float4 r2 = s_r2[j];
-        const float4 r3 = s_r3[j];
+        const float4 r1 = h ? b1 : a1;
+        const float4 r2 = lds128(sbase + 1024 + j * 16);
+        const float4 r3 = lds128(sbase + 1536 + j * 16);
         C0 = __fmaf_rn(__fmul_rn(r2.x, alpha), T, C0);
         C1 = __fmaf_rn(__fmul_rn(r2.y, alpha), T, C1);
         C2 = __fmaf_rn(__fmul_rn(r2.z, alpha), T, C2);
@@ -108,11 +149,11 @@ __global__ void __launch_bounds__(TILE_PIX) render_kernel(RenderArgs a) {
         N2 = __fmaf_rn(__fmul_rn(r3.y, alpha), T, N2);
         if (ED_T == 1) E0 = __fmaf_rn(__fmul_rn(r1.w, alpha), T, E0);
         if (ED_T < 0) {
-          const float* e = a.extra_attrs + (size_t)s_id[j] * ED;
+          const float* e = a.extra_attrs + (size_t)s_id[warp][j] * ED;
           for (int c = 0; c < ED; c++) Ex[c] = __fmaf_rn(__fmul_rn(__ldg(e + c), alpha), T, Ex[c]);
         }
         T = test_T;
-        last_contributor = (uint32_t)(base + j + 1);
+        last_contributor = (uint32_t)(cb + j + 1);
       }
     }
   }
@@ -136,10 +177,11 @@ __global__ void __launch_bounds__(TILE_PIX) render_kernel(RenderArgs a) {
 
 void launch_render(const RenderArgs& a, cudaStream_t s) {
   if (a.W <= 0 || a.H <= 0) return;
-  const dim3 grid(a.grid_x, a.grid_y);
-  if (a.ED == 0) render_kernel<0><<<grid, TILE_PIX, 0, s>>>(a);
-  else if (a.ED == 1) render_kernel<1><<<grid, TILE_PIX, 0, s>>>(a);
-  else render_kernel<-1><<<grid, TILE_PIX, 0, s>>>(a);
+  const int units = a.grid_x * a.grid_y * 8;
+  const int grid = (units + RW - 1) / RW;
+  if (a.ED == 0) render_kernel<0><<<grid, RT, 0, s>>>(a);
+  else if (a.ED == 1) render_kernel<1><<<grid, RT, 0, s>>>(a);
+  else render_kernel<-1><<<grid, RT, 0, s>>>(a);
   count_launch();
 }
 

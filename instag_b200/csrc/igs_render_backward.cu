@@ -20,13 +20,6 @@
 
 namespace igs {
 
-constexpr int BATCH = TILE_PIX;
-
-__device__ __forceinline__ void thread_pixel_b(int tid, int& lx, int& ly) {
-  const int w = tid >> 5, l = tid & 31;
-  lx = (w & 1) * 8 + (l & 7);
-  ly = (w >> 1) * 4 + (l >> 3);
-}
 
 // Sum 16 per-lane values over the warp; lane l returns the total of v[l>>1].
 __device__ __forceinline__ float warp_transpose_reduce16(const float (&v)[16], int lane) {
@@ -53,32 +46,59 @@ __device__ __forceinline__ float warp_transpose_reduce16(const float (&v)[16], i
   return w1 + __shfl_xor_sync(FULL, w1, 1);
 }
 
-template <int ED_T> // 0, 1, or -1 = generic
-__global__ void __launch_bounds__(TILE_PIX) render_backward_kernel(BwdRenderArgs a) {
-  __shared__ float4 s_r0[BATCH];
-  __shared__ float4 s_r1[BATCH];
-  __shared__ float4 s_r2[BATCH];
-  __shared__ float4 s_r3[BATCH];
-  __shared__ uint32_t s_id[BATCH];
-  __shared__ uint32_t s_max_contrib;
+constexpr int BW = 2;        // warps (8x4 pixel blocks) per CTA
+constexpr int BT = BW * 32;
 
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  int lx, ly;
-  thread_pixel_b(tid, lx, ly);
-  const int px = blockIdx.x * TILE + lx, py = blockIdx.y * TILE + ly;
+__device__ __forceinline__ float4 lds128b(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts128b(uint32_t addr, float4 v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+// Per-pixel state of the reverse walk.  The reference keeps one running "colour
+// behind me" per channel (accum_rec*, last_*, backward.cu:640-675) and sums
+// (c - accum)*dL_dpixel over the channels.  Both are linear, so ONE scalar recurrence on
+//   u = <attributes, dL_dpixel> + dL_dalpha_pixel
+// gives the same sum:  A <- last_alpha*u_last + (1-last_alpha)*A ;  dL_dalpha = (u - A)*T + bg term.
+struct PixelBack {
+  float T, A, u_last, last_alpha;
+};
+
+template <int ED_T> // 0, 1, or -1 = generic
+__global__ void __launch_bounds__(BT) render_backward_kernel(BwdRenderArgs a) {
+  __shared__ float4 s_rec[BW][4][32];
+  __shared__ uint32_t s_id[BW][32];
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int unit = blockIdx.x * BW + warp;
+  const int tile = unit >> 3, wb = unit & 7;
+  if (tile >= a.grid_x * a.grid_y) return;
+  const int tx = tile % a.grid_x, ty = tile / a.grid_x;
+  const int bx = tx * TILE + (wb & 1) * 8, by = ty * TILE + (wb >> 1) * 4;
+  const int px = bx + (lane & 7), py = by + (lane >> 3);
   const bool inside = px < a.W && py < a.H;
   const float pxf = (float)px, pyf = (float)py;
-  const float wx0 = (float)(blockIdx.x * TILE + (warp & 1) * 8), wx1 = wx0 + 7.f;
-  const float wy0 = (float)(blockIdx.y * TILE + (warp >> 1) * 4), wy1 = wy0 + 3.f;
+  const float wx0 = (float)bx, wx1 = wx0 + 7.f, wy0 = (float)by, wy1 = wy0 + 3.f;
   const size_t HW = (size_t)a.H * a.W, pix = (size_t)py * a.W + px;
-  const uint2 range = a.ranges[blockIdx.y * a.grid_x + blockIdx.x];
-  const int total = (int)(range.y - range.x);
+  const uint2 range = __ldg(a.ranges + tile);
   const int ED = ED_T < 0 ? a.ED : ED_T;
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(&s_rec[warp][0][0]);
+  const uint32_t smine = sbase + lane * 16;
+  const uint32_t sidb = (uint32_t)__cvta_generic_to_shared(&s_id[warp][0]);
 
-  const float T_final = inside ? __fsub_rn(1.f, a.out_alpha[pix]) : 0.f;
-  float T = T_final;
   const int last_contributor = inside ? (int)a.n_contrib[pix] : 0;
-
+  // nothing behind the last contributor of any of the warp's pixels matters
+  const int wmax = (int)__reduce_max_sync(0xffffffffu, (unsigned)last_contributor);
+  if (wmax == 0) return;
+  const float T_final = inside ? __fsub_rn(1.f, a.out_alpha[pix]) : 0.f;
   float dpc0 = 0, dpc1 = 0, dpc2 = 0, dpd = 0, dpn0 = 0, dpn1 = 0, dpn2 = 0, dpa = 0, dpe0 = 0;
   if (inside) {
     dpc0 = a.dL_dcolor[pix]; dpc1 = a.dL_dcolor[HW + pix]; dpc2 = a.dL_dcolor[2 * HW + pix];
@@ -87,102 +107,102 @@ __global__ void __launch_bounds__(TILE_PIX) render_backward_kernel(BwdRenderArgs
     dpa = a.dL_dalpha[pix];
     if (ED >= 1) dpe0 = a.dL_dextra[pix];
   }
-  // The reference keeps one running "colour behind me" per channel (accum_rec*, last_*,
-  // backward.cu:640-675) and sums (c - accum)*dL_dpixel over the channels.  Both are linear,
-  // so ONE scalar recurrence on  u = <attributes, dL_dpixel> + dL_dalpha_pixel  gives the same sum:
-  //   A <- last_alpha*u_last + (1-last_alpha)*A ;  dL_dalpha = (u - A)*T + background term.
-  float A = 0.f, u_last = 0.f, last_alpha = 0.f;
+  PixelBack st{T_final, 0.f, 0.f, 0.f};
   const float bg_dot = __ldg(a.bg) * dpc0 + __ldg(a.bg + 1) * dpc1 + __ldg(a.bg + 2) * dpc2;
+  const float nbgT = -T_final * bg_dot;
 
-  // nothing behind the last contributor of ANY pixel of the tile matters
-  if (tid == 0) s_max_contrib = 0;
-  __syncthreads();
-  const int warp_max = (int)__reduce_max_sync(0xffffffffu, (unsigned)last_contributor);
-  if (lane == 0) atomicMax(&s_max_contrib, (unsigned)warp_max);
-  __syncthreads();
-  const int block_max = (int)s_max_contrib;
+  // entry e of the reverse walk is list position wmax-1-e (= its `contributor` index)
+  const uint32_t* __restrict__ list = a.point_list + range.x;
+  uint32_t id_cur = 0, id_nxt = 0;
+  float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f), q1 = q0;
+  if (lane < wmax) id_cur = __ldg(list + (wmax - 1 - lane));
+  if (32 + lane < wmax) id_nxt = __ldg(list + (wmax - 33 - lane));
+  if (lane < wmax) {
+    q0 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4);
+    q1 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4 + 1);
+  }
 
-  // r = reversed index (0 = last instance of the tile); forward position = total - r
-  for (int rbase = total - block_max; rbase < total; rbase += BATCH) {
-    __syncthreads();
-    const int n = min(BATCH, total - rbase);
-    if (tid < n) {
-      const uint32_t id = __ldg(a.point_list + range.y - 1 - (rbase + tid));
-      const float4* rec = a.splat + (size_t)id * SPLAT_F4;
-      s_id[tid] = id;
-      s_r0[tid] = __ldg(rec);
-      s_r1[tid] = __ldg(rec + 1);
-      s_r2[tid] = __ldg(rec + 2);
-      s_r3[tid] = __ldg(rec + 3);
+  for (int cb = 0; cb < wmax; cb += 32) {
+    const bool live = cb + lane < wmax;
+    const bool hit = live && splat_may_touch(q0.x, q0.y, q0.z, q1.x, q1.y, 2.f * __logf(255.f * q0.w),
+                                             wx0, wx1, wy0, wy1);
+    unsigned m = __ballot_sync(0xffffffffu, hit);
+    const uint32_t id_mine = id_cur;
+    const float4 c0 = q0, c1 = q1;
+    id_cur = id_nxt;
+    if (cb + 32 + lane < wmax) {
+      q0 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4);
+      q1 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4 + 1);
     }
-    __syncthreads();
-    // first j this warp cares about: contributor = total - (rbase+j) - 1 < warp_max
-    const int j0 = max(0, total - rbase - warp_max);
-    for (int cb = j0 & ~31; cb < n; cb += 32) {
-      bool hit = false;
-      const int jl = cb + lane;
-      if (jl >= j0 && jl < n) {
-        const float4 q0 = s_r0[jl];
-        const float4 q1 = s_r1[jl];
-        hit = splat_may_touch(q0.x, q0.y, q0.z, q1.x, q1.y, s_r3[jl].z, wx0, wx1, wy0, wy1);
-      }
-      unsigned m = __ballot_sync(0xffffffffu, hit);
-      while (m) {
-        const int j = cb + __ffs(m) - 1;
-        m &= m - 1;
-        const int contributor = total - (rbase + j) - 1;
-        const float4 r1 = s_r1[j];
-        const float4 r0 = s_r0[j];
-        const float dx = __fsub_rn(r1.x, pxf), dy = __fsub_rn(r1.y, pyf);
-        const float power = gauss_power(r0.x, r0.y, r0.z, dx, dy);
-        const float G = expf(power);
-        const float alpha = fminf(0.99f, __fmul_rn(r0.w, G));
-        const bool valid = contributor < last_contributor && !(power > 0.0f) && !(alpha < ALPHA_MIN);
-        if (!__any_sync(0xffffffffu, valid)) continue;
-        // per-pixel partials; lanes that do not blend this splat contribute exact zeros
-        float weight = 0.f, gp = 0.f; // alpha*T ; G * dL/dalpha
-        if (valid) {
-          const float4 r2 = s_r2[j];
-          const float4 r3 = s_r3[j];
-          const float rc = __frcp_rn(__fsub_rn(1.f, alpha));
-          T = T * rc;                                   // reference backward.cu:612 (T / (1 - alpha))
-          weight = alpha * T;
-          float u = dpa;
-          u = fmaf(r2.x, dpc0, u); u = fmaf(r2.y, dpc1, u); u = fmaf(r2.z, dpc2, u);
-          u = fmaf(r1.z, dpd, u);
-          u = fmaf(r2.w, dpn0, u); u = fmaf(r3.x, dpn1, u); u = fmaf(r3.y, dpn2, u);
-          if (ED >= 1) u = fmaf(r1.w, dpe0, u);
-          if (ED_T < 0) {
-            const float* e = a.extra_attrs + (size_t)s_id[j] * ED;
-            for (int c = 1; c < ED; c++) u = fmaf(__ldg(e + c), a.dL_dextra[c * HW + pix], u);
-          }
-          A = fmaf(last_alpha, u_last - A, A);
-          u_last = u;
-          last_alpha = alpha;
-          // + background term, reference backward.cu:684-687
-          const float dL_dalpha = fmaf(u - A, T, -T_final * rc * bg_dot);
-          gp = G * dL_dalpha;
+    if (cb + 64 + lane < wmax) id_nxt = __ldg(list + (wmax - 65 - cb - lane));
+    if (m == 0) continue;
+    __syncwarp();
+    if (hit) {
+      const float4* rec = a.splat + (size_t)id_mine * SPLAT_F4;
+      const float4 c2 = __ldg(rec + 2), c3 = __ldg(rec + 3);
+      sts128b(smine, c0);
+      sts128b(smine + 512, c1);
+      sts128b(smine + 1024, c2);
+      sts128b(smine + 1536, c3);
+      s_id[warp][lane] = id_mine;
+    }
+    __syncwarp();
+    while (m) {
+      const int j = __ffs(m) - 1;
+      m &= m - 1;
+      const int contributor = wmax - 1 - cb - j;
+      const float4 r1 = lds128b(sbase + 512 + j * 16);
+      const float4 r0 = lds128b(sbase + j * 16);
+      const float dx = __fsub_rn(r1.x, pxf), dy = __fsub_rn(r1.y, pyf);
+      const float power = gauss_power(r0.x, r0.y, r0.z, dx, dy);
+      const float G = expf(power);
+      const float alpha = fminf(0.99f, __fmul_rn(r0.w, G));
+      const bool valid = contributor < last_contributor && !(power > 0.0f) && !(alpha < ALPHA_MIN);
+      if (!__any_sync(0xffffffffu, valid)) continue;
+      // per-pixel partials; lanes that do not blend this splat contribute exact zeros
+      float weight = 0.f, gp = 0.f; // alpha*T ; G * dL/dalpha
+      if (valid) {
+        const float4 r2 = lds128b(sbase + 1024 + j * 16);
+        const float4 r3 = lds128b(sbase + 1536 + j * 16);
+        const float rc = rcp_approx(__fsub_rn(1.f, alpha));
+        st.T = st.T * rc;                              // reference backward.cu:612 (T / (1 - alpha))
+        weight = alpha * st.T;
+        float u = dpa;
+        u = fmaf(r2.x, dpc0, u); u = fmaf(r2.y, dpc1, u); u = fmaf(r2.z, dpc2, u);
+        u = fmaf(r1.z, dpd, u);
+        u = fmaf(r2.w, dpn0, u); u = fmaf(r3.x, dpn1, u); u = fmaf(r3.y, dpn2, u);
+        if (ED >= 1) u = fmaf(r1.w, dpe0, u);
+        if (ED_T < 0) {
+          const float* e = a.extra_attrs + (size_t)s_id[warp][j] * ED;
+          for (int c = 1; c < ED; c++) u = fmaf(__ldg(e + c), a.dL_dextra[c * HW + pix], u);
         }
-        // moments of gp about the splat centre: the per-Gaussian kernel turns them into
-        // dL/dmean2D, dL/dconic and dL/dopacity (they only differ by per-Gaussian factors)
-        float v[16];
-        const float gx = gp * dx, gy = gp * dy;
-        v[0] = gx; v[1] = gy; v[2] = gx * dx; v[3] = gx * dy; v[4] = gy * dy; v[5] = gp;
-        v[6] = weight * dpc0; v[7] = weight * dpc1; v[8] = weight * dpc2; v[9] = weight * dpd;
-        v[10] = weight * dpn0; v[11] = weight * dpn1; v[12] = weight * dpn2;
-        v[13] = ED >= 1 ? weight * dpe0 : 0.f;
-        v[14] = 0.f; v[15] = 0.f;
-        const float tot = warp_transpose_reduce16(v, lane);
-        const uint32_t id = s_id[j];
-        const int k = lane >> 1;
-        if (!(lane & 1) && k < 13 + (ED >= 1 ? 1 : 0)) atomicAdd(a.accum + (size_t)id * ACC_F + k, tot);
-        if (ED_T < 0) { // channels 1.. : plain warp reduction into the side array
-          for (int c = 1; c < ED; c++) {
-            float gsum = valid ? weight * a.dL_dextra[c * HW + pix] : 0.f;
+        st.A = fmaf(st.last_alpha, st.u_last - st.A, st.A);
+        st.u_last = u;
+        st.last_alpha = alpha;
+        // + background term, reference backward.cu:684-687
+        const float dL_dalpha = fmaf(u - st.A, st.T, nbgT * rc);
+        gp = G * dL_dalpha;
+      }
+      // moments of gp about the splat centre: the per-Gaussian kernel turns them into
+      // dL/dmean2D, dL/dconic and dL/dopacity (they only differ by per-Gaussian factors)
+      float v[16];
+      const float gx = gp * dx, gy = gp * dy;
+      v[0] = gx; v[1] = gy; v[2] = gx * dx; v[3] = gx * dy; v[4] = gy * dy; v[5] = gp;
+      v[6] = weight * dpc0; v[7] = weight * dpc1; v[8] = weight * dpc2; v[9] = weight * dpd;
+      v[10] = weight * dpn0; v[11] = weight * dpn1; v[12] = weight * dpn2;
+      v[13] = ED >= 1 ? weight * dpe0 : 0.f;
+      v[14] = 0.f; v[15] = 0.f;
+      const float tot = warp_transpose_reduce16(v, lane);
+      uint32_t id;
+      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(id) : "r"(sidb + j * 4));
+      if (!(lane & 1) && (lane >> 1) < 13 + (ED >= 1 ? 1 : 0))
+        atomicAdd(a.accum + (size_t)id * ACC_F + (lane >> 1), tot);
+      if (ED_T < 0) { // channels 1.. : plain warp reduction into the side array
+        for (int c = 1; c < ED; c++) {
+          float gsum = valid ? weight * a.dL_dextra[c * HW + pix] : 0.f;
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) gsum += __shfl_xor_sync(0xffffffffu, gsum, o);
-            if (lane == 0) atomicAdd(a.accum_extra + (size_t)id * (ED - 1) + (c - 1), gsum);
-          }
+          for (int o = 16; o > 0; o >>= 1) gsum += __shfl_xor_sync(0xffffffffu, gsum, o);
+          if (lane == 0) atomicAdd(a.accum_extra + (size_t)id * (ED - 1) + (c - 1), gsum);
         }
       }
     }
@@ -191,10 +211,11 @@ __global__ void __launch_bounds__(TILE_PIX) render_backward_kernel(BwdRenderArgs
 
 void launch_render_backward(const BwdRenderArgs& a, cudaStream_t s) {
   if (a.W <= 0 || a.H <= 0) return;
-  const dim3 grid(a.grid_x, a.grid_y);
-  if (a.ED == 0) render_backward_kernel<0><<<grid, TILE_PIX, 0, s>>>(a);
-  else if (a.ED == 1) render_backward_kernel<1><<<grid, TILE_PIX, 0, s>>>(a);
-  else render_backward_kernel<-1><<<grid, TILE_PIX, 0, s>>>(a);
+  const int units = a.grid_x * a.grid_y * 8;
+  const int grid = (units + BW - 1) / BW;
+  if (a.ED == 0) render_backward_kernel<0><<<grid, BT, 0, s>>>(a);
+  else if (a.ED == 1) render_backward_kernel<1><<<grid, BT, 0, s>>>(a);
+  else render_backward_kernel<-1><<<grid, BT, 0, s>>>(a);
   count_launch();
 }
 

@@ -93,15 +93,16 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
-def algorithmic_bytes(P, N, HW, T, S=0, c=0, ED=1, passes=6):
-    """SURVEY.md 8(d) per-stage algorithmic bytes, with this library's record sizes:
-    preprocess reads 44(+12S) B and writes the 64 B splat record + radii/tiles/offsets (+1 clamp);
-    sort = (8+4) B read + written per pass (+ the duplicate's first write is in `duplicate`)."""
+def algorithmic_bytes(P, N, HW, T, S=0, c=0, ED=1):
+    """Per-stage algorithmic bytes with this library's record sizes (DESIGN.md "Kernels"):
+    preprocess reads 44(+12S) B and writes the 64 B splat record + radii/tiles/offsets (+1 clamp),
+    4 B of tile-count atomic per instance and the tile ranges; duplicate reads 24 B per Gaussian and
+    writes one 8 B word per instance (+ a 4 B cursor atomic); the tile sort reads the words and
+    writes point_list + keys; render reads 4+64 B per instance and writes the images."""
     return {
-        "preprocess": (44 + 12 * S + 64 + 12 + c) * P,
-        "duplicate": 20 * P + 12 * N,
-        "sort": passes * 24 * N,
-        "tile_ranges": 8 * N + 8 * T,
+        "preprocess": (44 + 12 * S + 64 + 12 + c) * P + 4 * N + 12 * T,
+        "duplicate": 24 * P + 12 * N,
+        "sort": 8 * N + 12 * N,
         "render": (4 + 64) * N + (4 * (8 + ED) + 4) * HW,
         "render_backward": (4 + 64) * N + (8 + 4 * (8 + ED)) * HW + 2 * 64 * P,
         "preprocess_backward": (64 + 64 + 44 + 12 * S + c + 4 * (26 + 3 * (S if S else 0) + ED)) * P,
@@ -355,7 +356,7 @@ def finish(a, cfg, sc, grads, arm, world, rank, ms, per, wall, value, e2e, clock
     alg = algorithmic_bytes(P, N, H * W, T, S=S_, c=1 if S_ else 0)
     table = {}
     for k, t in stages.items():
-        if t is None or t <= 0:
+        if t is None or t <= 0 or k not in alg:
             continue
         gbs = alg[k] / (t * 1e-3) / 1e9
         table[k] = {"ms": t, "alg_bytes": int(alg[k]), "gbs": gbs, "frac_hbm": gbs / hbm_peak}

@@ -85,7 +85,8 @@ typedef struct IgsFwdArgs {
   void* img;    /* [keep]    igs_img_bytes(W,H) */
   void* bin;    /* [keep]    igs_bin_bytes(capacity) */
   void* sort;   /* [scratch] igs_sort_bytes(capacity) */
-  void* ctrl;   /* [scratch] igs_ctrl_bytes(P,capacity): scan/sort look-back state */
+  void* ctrl;   /* [scratch] igs_ctrl_bytes(P,W,H): scan look-back state, tile counts and cursors;
+                 * must stay untouched between igs_forward and a following igs_forward_bin_render */
   int64_t capacity; /* instance capacity of bin/sort */
   /* pinned host slot the library copies num_rendered into */
   int32_t* num_rendered_pinned;
@@ -143,7 +144,7 @@ size_t igs_geom_bytes(int32_t P);
 size_t igs_img_bytes(int32_t W, int32_t H);
 size_t igs_bin_bytes(int64_t capacity);
 size_t igs_sort_bytes(int64_t capacity);
-size_t igs_ctrl_bytes(int32_t P, int64_t capacity);
+size_t igs_ctrl_bytes(int32_t P, int32_t W, int32_t H);
 size_t igs_accum_bytes(int32_t P, int32_t ED);
 
 /* Byte offsets of the arrays inside the workspaces (for tests / inspection).
@@ -163,7 +164,8 @@ void igs_img_layout(int32_t W, int32_t H, int64_t* off2);
  * the caller re-runs the second half with bigger bin/sort/ctrl buffers. */
 int igs_forward(const IgsFwdArgs* args, igs_stream_t stream, int64_t* num_rendered);
 
-/* Second half only (duplicate, sort, ranges, render), after IGS_ERR_CAPACITY. */
+/* Second half only (duplicate, tile sort, render), after IGS_ERR_CAPACITY: same geom / img /
+ * ctrl buffers as the call that overflowed, bigger bin / sort and capacity. */
 int igs_forward_bin_render(const IgsFwdArgs* args, igs_stream_t stream);
 
 int igs_backward(const IgsBwdArgs* args, igs_stream_t stream);
@@ -174,7 +176,7 @@ int igs_backward(const IgsBwdArgs* args, igs_stream_t stream);
  * thread (a ring of the last 256 frames); igs_profile_read waits for them and
  * returns the MEAN stage durations in ms over the *frames recorded since
  * igs_profile_enable(1) (-1 = stage did not run): 0 preprocess+scan, 1 duplicate (+ the 4-byte
- * num_rendered copy), 2 radix sort (all passes), 3 tile ranges, 4 render,
+ * num_rendered copy), 2 per-tile depth sort, 3 (unused: the tile ranges come out of stage 0), 4 render,
  * 5 render backward, 6 per-Gaussian backward.  igs_launch_count returns how
  * many kernels this host thread has launched through the library so far. */
 #define IGS_NUM_STAGES 7

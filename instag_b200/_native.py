@@ -60,7 +60,7 @@ SYMBOLS = {
     "igs_img_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "igs_bin_bytes": (C.c_size_t, [C.c_int64]),
     "igs_sort_bytes": (C.c_size_t, [C.c_int64]),
-    "igs_ctrl_bytes": (C.c_size_t, [C.c_int32, C.c_int64]),
+    "igs_ctrl_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
     "igs_accum_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "igs_geom_layout": (None, [C.c_int32, C.POINTER(C.c_int64)]),
     "igs_bin_layout": (None, [C.c_int64, C.POINTER(C.c_int64)]),

@@ -59,11 +59,6 @@ void prof_mark(int b, cudaStream_t s) {
 }
 void count_launch(int n) { g_launches += (unsigned long long)n; }
 
-static int num_passes(int grid_x, int grid_y) {
-  const int bits = 32 + higher_msb((uint32_t)(grid_x * grid_y)); // reference rasterizer_impl.cu:303-311
-  return (bits + RADIX_BITS - 1) / RADIX_BITS;
-}
-
 struct EventCache { // one reusable event per host thread
   cudaEvent_t ev = nullptr;
   cudaEvent_t get() {
@@ -100,7 +95,7 @@ static int validate_fwd(const IgsFwdArgs* a) {
 static PreArgs make_pre(const IgsFwdArgs* a) {
   PreArgs p{};
   const GeomLayout gl(a->P);
-  const CtrlLayout cl(a->P, a->capacity);
+  const CtrlLayout cl(a->P, a->W, a->H);
   char* g = (char*)a->geom;
   char* c = (char*)a->ctrl;
   p.P = a->P; p.D = a->D; p.M = a->M; p.ED = a->ED; p.W = a->W; p.H = a->H;
@@ -122,44 +117,50 @@ static PreArgs make_pre(const IgsFwdArgs* a) {
   p.clamped = (uint8_t*)(g + gl.clamped);
   p.scan_state = (unsigned long long*)(c + cl.scan_state);
   p.header = (CtrlHeader*)(c + cl.header);
+  p.tile_count = (uint32_t*)(c + cl.tile_count);
+  p.tile_cursor = (uint32_t*)(c + cl.tile_cursor);
+  p.ranges = (uint2*)((char*)a->img + ImgLayout(a->W, a->H).ranges);
   return p;
 }
 
-static int run_bin_render(const IgsFwdArgs* a, cudaStream_t s) {
+static BinArgs make_bin(const IgsFwdArgs* a) {
   const GeomLayout gl(a->P);
   const ImgLayout il(a->W, a->H);
   const BinLayout bl(a->capacity);
   const SortLayout sl(a->capacity);
-  const CtrlLayout cl(a->P, a->capacity);
+  const CtrlLayout cl(a->P, a->W, a->H);
   char* g = (char*)a->geom; char* im = (char*)a->img; char* b = (char*)a->bin;
   char* so = (char*)a->sort; char* c = (char*)a->ctrl;
-  const bool debug = a->debug != 0;
-
   BinArgs ba{};
   ba.P = a->P;
   ba.grid_x = (a->W + TILE - 1) / TILE; ba.grid_y = (a->H + TILE - 1) / TILE;
-  ba.passes = num_passes(ba.grid_x, ba.grid_y);
+  ba.num_tiles = ba.grid_x * ba.grid_y;
   ba.capacity = a->capacity;
   ba.radii = a->radii;
   ba.splat = (const float4*)(g + gl.splat);
-  ba.point_offsets = (const uint32_t*)(g + gl.point_offsets);
+  ba.tiles_touched = (const uint32_t*)(g + gl.tiles_touched);
   ba.header = (CtrlHeader*)(c + cl.header);
-  ba.hist = (uint32_t*)(c + cl.hist);
-  ba.lookback = (uint32_t*)(c + cl.lookback);
-  ba.sort_blocks = cl.sort_blocks;
-  // the LAST pass must land in the [keep] bin workspace: buffer index passes&1
-  const int keep = ba.passes & 1;
-  ba.keys[keep] = (uint64_t*)(b + bl.keys);       ba.vals[keep] = (uint32_t*)(b + bl.point_list);
-  ba.keys[keep ^ 1] = (uint64_t*)(so + sl.keys_alt); ba.vals[keep ^ 1] = (uint32_t*)(so + sl.vals_alt);
-  ba.ranges = (uint2*)(im + il.ranges);
-  ba.num_tiles = ba.grid_x * ba.grid_y;
+  ba.tile_cursor = (uint32_t*)(c + cl.tile_cursor);
+  ba.ranges = (const uint2*)(im + il.ranges);
+  ba.pairs = (unsigned long long*)(so + sl.pairs);
+  ba.point_list = (uint32_t*)(b + bl.point_list);
+  ba.keys = (uint64_t*)(b + bl.keys);
+  return ba;
+}
+
+static int run_bin_render(const IgsFwdArgs* a, cudaStream_t s) {
+  const ImgLayout il(a->W, a->H);
+  char* im = (char*)a->img;
+  const bool debug = a->debug != 0;
+  const BinArgs ba = make_bin(a);
   launch_binning(ba, s);
-  if (int r = stage_check(debug, s, "binning (duplicate/sort/ranges)")) return r;
+  if (int r = stage_check(debug, s, "binning (duplicate/tile sort)")) return r;
 
   RenderArgs ra{};
   ra.W = a->W; ra.H = a->H; ra.ED = a->ED; ra.grid_x = ba.grid_x; ra.grid_y = ba.grid_y;
+  ra.header = ba.header;
   ra.ranges = ba.ranges;
-  ra.point_list = (const uint32_t*)(b + bl.point_list);
+  ra.point_list = ba.point_list;
   ra.splat = ba.splat;
   ra.extra_attrs = a->extra_attrs;
   ra.bg = a->bg;
@@ -171,16 +172,10 @@ static int run_bin_render(const IgsFwdArgs* a, cudaStream_t s) {
   return stage_check(debug, s, "render");
 }
 
-// zero the look-back / histogram / ticket state; keeps header.num_rendered when asked
-static int reset_ctrl(const IgsFwdArgs* a, cudaStream_t s, bool keep_header) {
-  const CtrlLayout cl(a->P, a->capacity);
-  char* c = (char*)a->ctrl;
-  if (keep_header) {
-    CtrlHeader* h = (CtrlHeader*)(c + cl.header);
-    if (int r = check_cuda(cudaMemsetAsync(h->ticket, 0, sizeof(h->ticket), s), "memset ticket")) return r;
-    return check_cuda(cudaMemsetAsync(c + cl.hist, 0, cl.total - cl.hist, s), "memset ctrl");
-  }
-  return check_cuda(cudaMemsetAsync(c, 0, cl.total, s), "memset ctrl");
+// zero the scan state, the tile counts and the header
+static int reset_ctrl(const IgsFwdArgs* a, cudaStream_t s) {
+  const CtrlLayout cl(a->P, a->W, a->H);
+  return check_cuda(cudaMemsetAsync(a->ctrl, 0, cl.zeroed(), s), "memset ctrl");
 }
 
 } // namespace igs
@@ -196,7 +191,7 @@ size_t igs_geom_bytes(int32_t P) { return GeomLayout(P).total; }
 size_t igs_img_bytes(int32_t W, int32_t H) { return ImgLayout(W, H).total; }
 size_t igs_bin_bytes(int64_t capacity) { return BinLayout(capacity).total; }
 size_t igs_sort_bytes(int64_t capacity) { return SortLayout(capacity).total; }
-size_t igs_ctrl_bytes(int32_t P, int64_t capacity) { return CtrlLayout(P, capacity).total; }
+size_t igs_ctrl_bytes(int32_t P, int32_t W, int32_t H) { return CtrlLayout(P, W, H).total; }
 size_t igs_accum_bytes(int32_t P, int32_t ED) { return accum_bytes(P, ED); }
 
 void igs_geom_layout(int32_t P, int64_t* off) {
@@ -217,7 +212,7 @@ int igs_forward(const IgsFwdArgs* a, igs_stream_t stream, int64_t* num_rendered)
   cudaStream_t s = (cudaStream_t)stream;
   const bool debug = a->debug != 0;
   if (num_rendered) *num_rendered = 0;
-  if (int r = reset_ctrl(a, s, false)) return r;
+  if (int r = reset_ctrl(a, s)) return r;
   if (a->P == 0) { // reference rasterize_points.cu:93: outputs stay at their fill value
     const size_t HW = (size_t)a->W * a->H;
     cudaMemsetAsync(a->out_depth, 0, HW * 4, s); cudaMemsetAsync(a->out_alpha, 0, HW * 4, s);
@@ -250,12 +245,11 @@ int igs_forward(const IgsFwdArgs* a, igs_stream_t stream, int64_t* num_rendered)
 int igs_forward_bin_render(const IgsFwdArgs* a, igs_stream_t stream) {
   if (int r = validate_fwd(a)) return r;
   cudaStream_t s = (cudaStream_t)stream;
-  // new ctrl buffer: bring num_rendered over from the pinned slot
-  const CtrlLayout cl(a->P, a->capacity);
-  if (int r = check_cuda(cudaMemsetAsync(a->ctrl, 0, cl.total, s), "memset ctrl")) return r;
-  CtrlHeader* h = (CtrlHeader*)((char*)a->ctrl + cl.header);
-  if (int r = check_cuda(cudaMemcpyAsync(&h->num_rendered, a->num_rendered_pinned, sizeof(int32_t),
-                                         cudaMemcpyHostToDevice, s), "restore num_rendered")) return r;
+  // same geom / img / ctrl as the igs_forward that overflowed (tile ranges and counts are
+  // still valid), bigger bin / sort: clear the overflow flag, rewind the tile cursors
+  const BinArgs ba = make_bin(a);
+  if (int r = check_cuda(cudaMemsetAsync(&ba.header->overflow, 0, sizeof(uint32_t), s), "clear overflow")) return r;
+  launch_reset_cursors(ba, s);
   return run_bin_render(a, s);
 }
 

@@ -1,257 +1,228 @@
-// Stages 2+3 of the forward path and the first half of stage 4:
-//   duplicate_kernel   instance-parallel tile-key duplication (reference
-//                      duplicateWithKeys, rasterizer_impl.cu:70-111) fused with
-//                      the digit histograms of every radix pass;
-//   onesweep_kernel    hand-written stable LSD radix sort of the 64-bit
-//                      tile|depth keys, one launch per 8-bit digit, chained
-//                      decoupled look-back (replaces cub::DeviceRadixSort::
-//                      SortPairs, rasterizer_impl.cu:306-311);
-//   tile_ranges_kernel identifyTileRanges (rasterizer_impl.cu:116-138) incl.
-//                      the zero fill of the ranges.
-// num_rendered lives on the device (CtrlHeader): no kernel here needs the host
-// to know it, grids are sized by the caller's capacity.
+// Stages 2+3 of the forward path: binning.
 //
-// Bound: HBM.  Algorithmic bytes: duplicate 20P + 12N; sort (8+4)*2*N per pass;
-// ranges 8N + 8T.
+// The reference duplicates every Gaussian into one (tile|depth) key per covered
+// tile, sorts ALL keys with a 6-pass device-wide radix sort and then finds the
+// tile boundaries (duplicateWithKeys, rasterizer_impl.cu:70-111;
+// cub::DeviceRadixSort::SortPairs, :306-311; identifyTileRanges, :116-138).
+// The result is fully specified -- instances ordered by (tile, depth bits,
+// emission order) -- so any algorithm that produces exactly that order is a
+// drop-in.  Here the tile part of the sort is done by COUNTING:
+//   preprocess_kernel   counts the instances of every tile while it computes the
+//                       tile rectangles, and its last CTA turns the counts into
+//                       the tile ranges (igs_preprocess.cu);
+//   duplicate_kernel    drops every instance straight into its tile's segment
+//                       (slot = atomic cursor of the tile), as one 64-bit word
+//                       depth_bits<<32 | gaussian_id;
+//   tile_sort_kernel    one CTA per tile sorts the segment by that word in shared
+//                       memory and writes point_list (+ the reference's 64-bit keys).
+// Sorting by (depth, id) reproduces the reference's stable order: inside one tile
+// the emission order of the reference is ascending Gaussian id (a Gaussian meets
+// a tile at most once), and the words are unique, so the order inside a segment
+// before the sort does not matter.
+//
+// Bound: HBM/L2 latency.  Algorithmic bytes: duplicate 24P + 8N (+ 4N atomics),
+// tile sort 8N read + 12N written.
 #include "igs_common.cuh"
 #include "igs_kernels.cuh"
 
 namespace igs {
 
 constexpr int DUP_THREADS = 256;
-constexpr int DUP_ITEMS = 8;
-constexpr int DUP_TILE = DUP_THREADS * DUP_ITEMS;
 
-// One thread per INSTANCE (coalesced key/value stores, no per-Gaussian loop
-// imbalance): instance i belongs to the Gaussian g with
-// point_offsets[g-1] <= i < point_offsets[g].
+// One warp per 32 Gaussians; the warp's instances are spread evenly over the lanes
+// (a lane finds the Gaussian that owns instance k by a 5-step search over the warp's
+// inclusive counts), so a screen-filling Gaussian does not serialise a thread.
 __global__ void __launch_bounds__(DUP_THREADS) duplicate_kernel(BinArgs a) {
-  __shared__ uint32_t s_hist[MAX_PASSES][RADIX];
-  const int tid = threadIdx.x;
-  for (int k = tid; k < a.passes * RADIX; k += DUP_THREADS) (&s_hist[0][0])[k] = 0;
-  __syncthreads();
-  const uint32_t N = min((int64_t)a.header->num_rendered, a.capacity);
-  const uint32_t base = blockIdx.x * DUP_TILE;
-  if (base < N) {
-    // Gaussian owning the first instance of this CTA's chunk: upper_bound
-    int lo = 0, hi = a.P; // first g with offsets[g] > base
-    while (lo < hi) {
-      const int mid = (lo + hi) >> 1;
-      if (__ldg(a.point_offsets + mid) > base) hi = mid; else lo = mid + 1;
+  const int lane = threadIdx.x & 31;
+  const int g = (blockIdx.x * DUP_THREADS + threadIdx.x);
+  uint32_t n = 0, xy = 0, w = 1, depth = 0;
+  if (g < a.P) n = __ldg(a.tiles_touched + g);
+  if (n) {
+    const float4 r1 = __ldg(a.splat + (size_t)g * SPLAT_F4 + 1); // x, y, depth, extra0
+    int x0, y0, x1, y1;
+    tile_rect(r1.x, r1.y, __ldg(a.radii + g), a.grid_x, a.grid_y, x0, y0, x1, y1);
+    xy = (uint32_t)x0 | ((uint32_t)y0 << 16);
+    w = (uint32_t)(x1 - x0);
+    depth = __float_as_uint(r1.z);
+  }
+  uint32_t incl = n;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+  const uint32_t excl = incl - n;
+  const int gbase = g - lane;
+  for (uint32_t kb = 0; kb < total; kb += 32) {
+    const uint32_t k = kb + lane;
+    // owner = number of lanes whose inclusive count is <= k
+    int o = 0;
+#pragma unroll
+    for (int step = 16; step > 0; step >>= 1) {
+      const uint32_t v = __shfl_sync(0xffffffffu, incl, o + step - 1);
+      if (v <= k) o += step;
     }
-    const int g_first = lo;
-#pragma unroll 1
-    for (int it = 0; it < DUP_ITEMS; it++) {
-      const uint32_t i = base + it * DUP_THREADS + tid;
-      if (i >= N) break;
-      // search forward from the CTA's first Gaussian: galloping + bisection
-      int l = g_first, step = 1, h = g_first;
-      while (h < a.P && __ldg(a.point_offsets + h) <= i) { l = h + 1; h += step; step <<= 1; }
-      if (h > a.P) h = a.P;
-      while (l < h) {
-        const int mid = (l + h) >> 1;
-        if (__ldg(a.point_offsets + mid) > i) h = mid; else l = mid + 1;
-      }
-      const int g = l;
-      const uint32_t start = g == 0 ? 0u : __ldg(a.point_offsets + g - 1);
-      const float4 r1 = __ldg(a.splat + (size_t)g * SPLAT_F4 + 1); // x, y, depth, extra0
-      int x0, y0, x1, y1;
-      tile_rect(r1.x, r1.y, __ldg(a.radii + g), a.grid_x, a.grid_y, x0, y0, x1, y1);
-      const uint32_t local = i - start, w = (uint32_t)(x1 - x0);
-      const uint32_t ty = y0 + local / w, tx = x0 + local % w;
-      const uint64_t key = ((uint64_t)(ty * a.grid_x + tx) << 32) | __float_as_uint(r1.z);
-      a.keys[0][i] = key;
-      a.vals[0][i] = (uint32_t)g;
-      for (int p = 0; p < a.passes; p++) atomicAdd(&s_hist[p][(key >> (RADIX_BITS * p)) & (RADIX - 1)], 1u);
+    o = min(o, 31);
+    const uint32_t o_excl = __shfl_sync(0xffffffffu, excl, o);
+    const uint32_t o_xy = __shfl_sync(0xffffffffu, xy, o);
+    const uint32_t o_w = __shfl_sync(0xffffffffu, w, o);
+    const uint32_t o_depth = __shfl_sync(0xffffffffu, depth, o);
+    if (k < total) {
+      const uint32_t local = k - o_excl;
+      const uint32_t row = local / o_w, col = local - row * o_w;
+      const uint32_t t = ((o_xy >> 16) + row) * (uint32_t)a.grid_x + (o_xy & 0xffffu) + col;
+      const uint32_t slot = atomicAdd(a.tile_cursor + t, 1u);
+      if ((int64_t)slot < a.capacity)
+        a.pairs[slot] = ((unsigned long long)o_depth << 32) | (uint32_t)(gbase + o);
     }
   }
-  __syncthreads();
-  for (int k = tid; k < a.passes * RADIX; k += DUP_THREADS) {
-    const uint32_t c = (&s_hist[0][0])[k];
-    if (c) atomicAdd(a.hist + k, c);
-  }
 }
 
-// lookback word: high 2 bits = flag (1 aggregate, 2 inclusive prefix), low 30 = count
-constexpr uint32_t LB_AGG = 1u << 30, LB_PREFIX = 2u << 30, LB_MASK = (1u << 30) - 1;
-
-__device__ __forceinline__ uint32_t ld_relaxed(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_relaxed(uint32_t* p, uint32_t v) {
-  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+__global__ void reset_cursors_kernel(BinArgs a) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= a.num_tiles) return;
+  // start of the segment = exclusive prefix of the counts; recomputed from the ranges of the
+  // non-empty tiles is not possible for empty ones, but those never receive an instance
+  a.tile_cursor[t] = a.ranges[t].x;
 }
 
-// One 8-bit digit pass.  Stability: keys are read warp-striped (a warp owns a
-// contiguous chunk, item-major / lane-minor = memory order) and ranked with
-// match_any in that order; warps and CTAs are ordered by prefix sums.
-__global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(
-    const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, uint64_t* __restrict__ kout,
-    uint32_t* __restrict__ vout, const uint32_t* __restrict__ hist, uint32_t* lookback, CtrlHeader* header,
-    int pass, int64_t capacity) {
-  constexpr int WARPS = SORT_THREADS / 32;
-  __shared__ uint32_t s_warp_hist[WARPS][RADIX];
-  __shared__ uint64_t s_keys[SORT_TILE];
-  __shared__ uint32_t s_vals[SORT_TILE];
-  __shared__ uint32_t s_local_start[RADIX];  // exclusive digit offsets inside this CTA
-  __shared__ uint32_t s_global_base[RADIX];  // where this CTA's run of each digit starts in the output
-  __shared__ uint32_t s_scan[WARPS];
-  __shared__ uint32_t s_bid;
+// ---- per-tile sort --------------------------------------------------------------------
+constexpr int TS_THREADS = 256;
+constexpr int TS_CAP = 4096;      // largest segment sorted in shared memory
+constexpr int TS_BUCKETS = 2048;  // most buckets of the distribution pass (40 KB of shared memory in all)
+
+// Segments are sorted by ONE distribution pass: depth bits are mapped monotonically onto
+// ~n buckets between the segment's min and max (so a bucket holds ~1-2 words), a counting
+// pass groups the words by bucket, and every word then finds its rank among the few words
+// of its own bucket.  O(n) for any spread-out depth distribution; a segment whose depths
+// all collide degrades to O(n^2 / threads) but stays exact.
+__global__ void __launch_bounds__(TS_THREADS) tile_sort_kernel(BinArgs a) {
+  __shared__ unsigned long long s_word[TS_CAP];
+  __shared__ uint32_t s_cnt[TS_BUCKETS];
+  __shared__ uint32_t s_red[2][TS_THREADS / 32];
+  __shared__ uint32_t s_part[TS_THREADS / 32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int shift = RADIX_BITS * pass;
+  const int tile = blockIdx.x;
+  const uint2 range = a.ranges[tile];
+  const int n = (int)(range.y - range.x);
+  if (n == 0 || a.header->overflow) return;
+  unsigned long long* seg = a.pairs + range.x;
+  uint32_t* __restrict__ out_id = a.point_list + range.x;
+  uint64_t* __restrict__ out_key = a.keys + range.x;
+  const uint64_t tile_hi = (uint64_t)tile << 32;
 
-  const uint32_t N = min((int64_t)header->num_rendered, capacity);
-  const uint32_t num_tiles = (N + SORT_TILE - 1) / SORT_TILE;
-  if (tid == 0) s_bid = atomicAdd(&header->ticket[pass], 1u);
-  for (int k = tid; k < WARPS * RADIX; k += SORT_THREADS) (&s_warp_hist[0][0])[k] = 0;
-  __syncthreads();
-  const uint32_t bid = s_bid;
-  if (bid >= num_tiles) return;
-
-  // ---- load (warp-striped) and rank within the warp ----
-  const uint32_t warp_base = bid * SORT_TILE + warp * (32 * SORT_ITEMS);
-  uint64_t key[SORT_ITEMS];
-  uint32_t rank[SORT_ITEMS];
-  const unsigned lt_mask = (1u << lane) - 1;
-#pragma unroll
-  for (int it = 0; it < SORT_ITEMS; it++) {
-    const uint32_t i = warp_base + it * 32 + lane;
-    key[it] = i < N ? kin[i] : ~0ull;
-  }
-#pragma unroll
-  for (int it = 0; it < SORT_ITEMS; it++) {
-    const uint32_t i = warp_base + it * 32 + lane;
-    const bool valid = i < N;
-    const uint32_t d = (uint32_t)(key[it] >> shift) & (RADIX - 1);
-    const unsigned peers = __match_any_sync(0xffffffffu, valid ? d : RADIX);
-    const int leader = __ffs(peers) - 1;
-    uint32_t pre = 0;
-    if (valid && lane == leader) {
-      pre = s_warp_hist[warp][d];
-      s_warp_hist[warp][d] = pre + __popc(peers);
-    }
-    pre = __shfl_sync(0xffffffffu, pre, leader);
-    rank[it] = pre + __popc(peers & lt_mask);
-    __syncwarp();
-  }
-  __syncthreads();
-
-  // ---- per digit (thread d): warp offsets, CTA count, chained look-back ----
-  uint32_t count = 0;
-  {
-    const int d = tid;
-#pragma unroll
-    for (int w = 0; w < WARPS; w++) {
-      const uint32_t t = s_warp_hist[w][d];
-      s_warp_hist[w][d] = count;
-      count += t;
-    }
-    uint32_t* my = lookback + (size_t)bid * RADIX + d;
-    uint32_t excl = 0;
-    if (bid == 0) {
-      st_relaxed(my, LB_PREFIX | count);
-    } else {
-      st_relaxed(my, LB_AGG | count);
-      int j = (int)bid - 1;
-      while (true) {
-        const uint32_t v = ld_relaxed(lookback + (size_t)j * RADIX + d);
-        if ((v >> 30) == 0) continue; // not published yet
-        excl += v & LB_MASK;
-        if ((v >> 30) == 2) break;
-        j--;
+  if (n > TS_CAP) {
+    // rare: in-place bitonic network over the segment in global memory (arbitrary n: elements
+    // beyond n are virtual +inf, every compare-exchange keeps the smaller word at the lower index)
+    for (unsigned k = 2; (k >> 1) < (unsigned)n; k <<= 1) {
+      for (unsigned d = k >> 1; d > 0; d >>= 1) {
+        __syncthreads();
+        for (unsigned i = tid; i < (unsigned)n; i += TS_THREADS) {
+          if (i & d) continue; // i is the lower index of its pair
+          const unsigned j = (d == (k >> 1)) ? (i ^ (k - 1)) : (i | d); // first step of a merge mirrors
+          if (j >= (unsigned)n) continue;
+          const unsigned long long x = __ldcg(seg + i), y = __ldcg(seg + j);
+          if (x > y) { __stcg(seg + i, y); __stcg(seg + j, x); }
+        }
       }
-      st_relaxed(my, LB_PREFIX | (excl + count));
     }
-    // global digit start = exclusive scan of the pass histogram (256 bins)
-    const uint32_t h = __ldg(hist + pass * RADIX + d);
-    uint32_t hs = h, cs = count;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t n1 = __shfl_up_sync(0xffffffffu, hs, o), n2 = __shfl_up_sync(0xffffffffu, cs, o);
-      if (lane >= o) { hs += n1; cs += n2; }
+    __syncthreads();
+    for (int i = tid; i < n; i += TS_THREADS) {
+      const unsigned long long wd = __ldcg(seg + i);
+      out_id[i] = (uint32_t)wd;
+      out_key[i] = tile_hi | (wd >> 32);
     }
-    // two interleaved block scans share s_scan via two rounds
-    if (lane == 31) s_scan[warp] = hs;
-    __syncthreads();
-    uint32_t hoff = 0;
-    for (int w = 0; w < warp; w++) hoff += s_scan[w];
-    __syncthreads();
-    if (lane == 31) s_scan[warp] = cs;
-    __syncthreads();
-    uint32_t coff = 0;
-    for (int w = 0; w < warp; w++) coff += s_scan[w];
-    const uint32_t local_start = coff + cs - count;
-    s_local_start[d] = local_start;
-    s_global_base[d] = (hoff + hs - h) + excl - local_start; // add the position inside the CTA to get the output index
-  }
-  __syncthreads();
-
-  // ---- place into shared memory in sorted order, then coalesced scatter ----
-#pragma unroll
-  for (int it = 0; it < SORT_ITEMS; it++) {
-    const uint32_t i = warp_base + it * 32 + lane;
-    if (i < N) {
-      const uint32_t d = (uint32_t)(key[it] >> shift) & (RADIX - 1);
-      const uint32_t pos = s_local_start[d] + s_warp_hist[warp][d] + rank[it];
-      s_keys[pos] = key[it];
-      s_vals[pos] = vin[i];
-    }
-  }
-  __syncthreads();
-  const uint32_t tile_count = min((uint32_t)SORT_TILE, N - bid * SORT_TILE);
-  for (uint32_t p = tid; p < tile_count; p += SORT_THREADS) {
-    const uint64_t k = s_keys[p];
-    const uint32_t d = (uint32_t)(k >> shift) & (RADIX - 1);
-    const uint32_t dst = s_global_base[d] + p;
-    kout[dst] = k;
-    vout[dst] = s_vals[p];
-  }
-}
-
-// ranges[t] = [first, last+1) of tile t in the sorted list, (0,0) if empty.
-// One thread per tile boundary candidate: thread i looks at keys[i-1], keys[i].
-__global__ void tile_ranges_kernel(const uint64_t* __restrict__ keys, const CtrlHeader* header, int64_t capacity,
-                                   uint2* ranges, int num_tiles) {
-  const uint32_t N = min((int64_t)header->num_rendered, capacity);
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  // tiles that own no instance keep (0,0): fill the gaps between consecutive
-  // tile ids here instead of a separate memset (reference rasterizer_impl.cu:313)
-  if (N == 0) {
-    if (i < (uint32_t)num_tiles) ranges[i] = make_uint2(0, 0);
     return;
   }
-  if (i > N) return;
-  const int cur = i < N ? (int)(keys[i] >> 32) : num_tiles;       // virtual end marker
-  const int prev = i > 0 ? (int)(keys[i - 1] >> 32) : -1;        // virtual start marker
-  if (cur != prev) {
-    if (i < N) ranges[cur].x = i;
-    if (i > 0) ranges[prev].y = i;
-    for (int t = prev + 1; t < cur && t < num_tiles; t++) ranges[t] = make_uint2(0, 0);
+
+  // ---- min / max of the depth bits ----
+  uint32_t lo = 0xffffffffu, hi = 0u;
+  for (int i = tid; i < n; i += TS_THREADS) {
+    const uint32_t d = (uint32_t)(seg[i] >> 32);
+    lo = min(lo, d); hi = max(hi, d);
   }
+  lo = __reduce_min_sync(0xffffffffu, lo);
+  hi = __reduce_max_sync(0xffffffffu, hi);
+  if (lane == 0) { s_red[0][warp] = lo; s_red[1][warp] = hi; }
+  int nb = 32;
+  while (nb < n) nb <<= 1;            // ~1 word per bucket
+  nb = min(nb, TS_BUCKETS);
+  for (int b = tid; b < nb; b += TS_THREADS) s_cnt[b] = 0;
+  __syncthreads();
+#pragma unroll
+  for (int w = 0; w < TS_THREADS / 32; w++) { lo = min(lo, s_red[0][w]); hi = max(hi, s_red[1][w]); }
+  // bucket(d) = (d - lo) >> shift with the smallest shift that keeps (hi - lo) >> shift < nb:
+  // monotone in d, between nb/2 and nb buckets in use.  (A 32.32 fixed-point multiply would fill
+  // the buckets evenly, but nvcc 12.9 folds `((u64)x * m >> 32) * 4` into `x * (m >> 30)` when it
+  // becomes a shared-memory index -- wrong, and it faulted; a shift cannot be mis-folded.)
+  const int need = 32 - __clz(hi - lo), have = 31 - __clz(nb); // bits of the largest offset, log2(nb)
+  const int shift = need > have ? need - have : 0;
+#define TS_BUCKET(d) (((d) - lo) >> shift)
+
+  // ---- count ----
+  for (int i = tid; i < n; i += TS_THREADS) atomicAdd(&s_cnt[TS_BUCKET((uint32_t)(seg[i] >> 32))], 1u);
+  __syncthreads();
+  // ---- exclusive scan of the counts (each thread owns nb/256 consecutive buckets) ----
+  {
+    const int per = nb / TS_THREADS > 0 ? nb / TS_THREADS : 1; // nb is a power of two >= 32
+    const int b0 = tid * per;
+    uint32_t sum = 0;
+    if (b0 < nb)
+      for (int b = 0; b < per; b++) sum += s_cnt[b0 + b];
+    uint32_t inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += v;
+    }
+    if (lane == 31) s_part[warp] = inc;
+    __syncthreads();
+    uint32_t run = inc - sum;
+    for (int w = 0; w < warp; w++) run += s_part[w];
+    if (b0 < nb)
+      for (int b = 0; b < per; b++) {
+        const uint32_t c = s_cnt[b0 + b];
+        s_cnt[b0 + b] = run; // start of the bucket; becomes its end after the scatter
+        run += c;
+      }
+  }
+  __syncthreads();
+  // ---- scatter into bucket order ----
+  for (int i = tid; i < n; i += TS_THREADS) {
+    const unsigned long long wd = seg[i];
+    const uint32_t slot = atomicAdd(&s_cnt[TS_BUCKET((uint32_t)(wd >> 32))], 1u);
+    s_word[slot] = wd;
+  }
+  __syncthreads();
+  // ---- rank inside the bucket, write out ----
+  for (int p = tid; p < n; p += TS_THREADS) {
+    const unsigned long long wd = s_word[p];
+    const uint32_t b = TS_BUCKET((uint32_t)(wd >> 32));
+    const uint32_t start = b ? s_cnt[b - 1] : 0u, end = s_cnt[b];
+    uint32_t rank = 0;
+    for (uint32_t q = start; q < end; q++) rank += s_word[q] < wd ? 1u : 0u;
+    const uint32_t dst = start + rank;
+    out_id[dst] = (uint32_t)wd;
+    out_key[dst] = tile_hi | (wd >> 32);
+  }
+#undef TS_BUCKET
 }
 
 void launch_binning(const BinArgs& a, cudaStream_t s) {
-  if (a.P <= 0 || a.capacity <= 0) {
-    if (a.num_tiles > 0) cudaMemsetAsync(a.ranges, 0, sizeof(uint2) * a.num_tiles, s);
-    return;
-  }
-  const int dup_blocks = (int)((a.capacity + DUP_TILE - 1) / DUP_TILE);
-  duplicate_kernel<<<dup_blocks, DUP_THREADS, 0, s>>>(a);
+  if (a.P <= 0 || a.num_tiles <= 0) return;
+  duplicate_kernel<<<(a.P + DUP_THREADS - 1) / DUP_THREADS, DUP_THREADS, 0, s>>>(a);
   prof_mark(2, s);
-  for (int p = 0; p < a.passes; p++) {
-    const int in = p & 1, out = in ^ 1;
-    onesweep_kernel<<<a.sort_blocks, SORT_THREADS, 0, s>>>(a.keys[in], a.vals[in], a.keys[out], a.vals[out],
-                                                           a.hist, a.lookback + (size_t)p * a.sort_blocks * RADIX,
-                                                           a.header, p, a.capacity);
-  }
+  tile_sort_kernel<<<a.num_tiles, TS_THREADS, 0, s>>>(a);
   prof_mark(3, s);
-  const uint64_t* sorted = a.keys[a.passes & 1];
-  const int64_t threads = a.capacity + 1 > a.num_tiles ? a.capacity + 1 : a.num_tiles;
-  tile_ranges_kernel<<<(int)((threads + 255) / 256), 256, 0, s>>>(sorted, a.header, a.capacity, a.ranges, a.num_tiles);
   prof_mark(4, s);
-  count_launch(2 + a.passes);
+  count_launch(2);
+}
+
+void launch_reset_cursors(const BinArgs& a, cudaStream_t s) {
+  if (a.num_tiles <= 0) return;
+  reset_cursors_kernel<<<(a.num_tiles + 255) / 256, 256, 0, s>>>(a);
+  count_launch(1);
 }
 
 } // namespace igs

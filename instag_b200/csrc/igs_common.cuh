@@ -64,46 +64,39 @@ struct BinLayout { // sorted result, kept for backward
   }
 };
 
-struct SortLayout { // ping-pong partner of BinLayout, scratch
-  size_t vals_alt, keys_alt, total;
+struct SortLayout { // unsorted (depth|id) pairs grouped by tile, scratch
+  size_t pairs, total;
   __host__ __device__ explicit SortLayout(int64_t cap) {
     size_t c = (size_t)(cap > 0 ? cap : 1), o = 0;
-    vals_alt = o;  o = align_up(o + c * sizeof(uint32_t));
-    keys_alt = o;  o = align_up(o + c * sizeof(uint64_t));
+    pairs = o;  o = align_up(o + c * sizeof(uint64_t));
     total = o;
   }
 };
 
-// radix sort geometry
-constexpr int RADIX_BITS = 8;
-constexpr int RADIX = 1 << RADIX_BITS;
-constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 8;                          // keys per thread
-constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;   // keys per CTA per pass
-constexpr int MAX_PASSES = 8;
 constexpr int PRE_THREADS = 256;
 
 struct CtrlHeader {
-  uint32_t num_rendered;       // written by the preprocess kernel's last CTA
-  uint32_t overflow;           // num_rendered > capacity
-  uint32_t ticket[MAX_PASSES]; // dynamic CTA ids of the onesweep passes
-  uint32_t pad[6];
+  uint32_t num_rendered;  // written by the preprocess CTA that owns the last Gaussians
+  uint32_t overflow;      // num_rendered > capacity
+  uint32_t ticket;        // dynamic CTA ids of the preprocess kernel (scan order = start order)
+  uint32_t done;          // preprocess CTAs that have finished; the last one scans the tile counts
+  uint32_t pad[4];
 };
 
 struct CtrlLayout {
-  size_t header, scan_state, hist, lookback, total;
-  int sort_blocks;
-  __host__ __device__ CtrlLayout(int P, int64_t cap) {
+  size_t header, scan_state, tile_count, tile_cursor, total;
+  __host__ __device__ CtrlLayout(int P, int W, int H) {
     size_t o = 0;
-    int pre_blocks = (P + PRE_THREADS - 1) / PRE_THREADS;
-    sort_blocks = (int)((cap + SORT_TILE - 1) / SORT_TILE);
-    if (sort_blocks < 1) sort_blocks = 1;
-    header = o;      o = align_up(o + sizeof(CtrlHeader));
-    scan_state = o;  o = align_up(o + (size_t)(pre_blocks ? pre_blocks : 1) * sizeof(unsigned long long));
-    hist = o;        o = align_up(o + (size_t)MAX_PASSES * RADIX * sizeof(uint32_t));
-    lookback = o;    o = align_up(o + (size_t)MAX_PASSES * sort_blocks * RADIX * sizeof(uint32_t));
+    const int pre_blocks = (P + PRE_THREADS - 1) / PRE_THREADS;
+    const size_t T = (size_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
+    header = o;       o = align_up(o + sizeof(CtrlHeader));
+    scan_state = o;   o = align_up(o + (size_t)(pre_blocks ? pre_blocks : 1) * sizeof(unsigned long long));
+    tile_count = o;   o = align_up(o + (T ? T : 1) * sizeof(uint32_t));
+    tile_cursor = o;  o = align_up(o + (T ? T : 1) * sizeof(uint32_t));
     total = o;
   }
+  // everything before tile_cursor is zeroed at the start of a frame
+  __host__ __device__ size_t zeroed() const { return tile_cursor; }
 };
 
 inline size_t accum_bytes(int P, int ED) {

@@ -18,29 +18,28 @@ struct PreArgs {
   uint8_t* clamped;
   unsigned long long* scan_state;
   CtrlHeader* header;
+  uint32_t* tile_count;   // [T] instances per tile (atomics), zeroed by the caller
+  uint32_t* tile_cursor;  // [T] next free slot of each tile segment (written by the last CTA)
+  uint2* ranges;          // [T] [start, end) of each tile in the sorted list, (0,0) if empty
 };
 
 struct BinArgs {
-  int P, grid_x, grid_y;
-  int passes;          // 8-bit digit passes covering 32 + tile bits
+  int P, grid_x, grid_y, num_tiles;
   int64_t capacity;
   const int32_t* radii;
   const float4* splat;
-  const uint32_t* point_offsets;
+  const uint32_t* tiles_touched;
   CtrlHeader* header;
-  uint32_t* hist;      // [MAX_PASSES][256]
-  uint32_t* lookback;  // [passes][sort_blocks][256]
-  int sort_blocks;
-  // ping-pong buffers; buf 0 receives the duplicated keys, the last pass
-  // writes into (keys_out, vals_out) = the [keep] bin workspace
-  uint64_t* keys[2];
-  uint32_t* vals[2];
-  uint2* ranges;       // [T]
-  int num_tiles;
+  uint32_t* tile_cursor;      // [T]
+  const uint2* ranges;        // [T]
+  unsigned long long* pairs;  // [capacity] (depth bits << 32 | gaussian id), grouped by tile, unordered inside
+  uint32_t* point_list;       // [capacity] sorted
+  uint64_t* keys;             // [capacity] sorted (tile << 32 | depth bits)
 };
 
 struct RenderArgs {
   int W, H, ED, grid_x, grid_y;
+  const CtrlHeader* header; // overflow flag: the tile lists are incomplete, render nothing
   const uint2* ranges;
   const uint32_t* point_list;
   const float4* splat;
@@ -80,7 +79,8 @@ struct BwdPreArgs {
 
 void launch_preprocess(const PreArgs& a, cudaStream_t s);
 void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s);
-void launch_binning(const BinArgs& a, cudaStream_t s);     // duplicate + sort + ranges
+void launch_binning(const BinArgs& a, cudaStream_t s);     // duplicate into tile segments + per-tile depth sort
+void launch_reset_cursors(const BinArgs& a, cudaStream_t s); // tile_cursor <- ranges.x (re-run after IGS_ERR_CAPACITY)
 void launch_render(const RenderArgs& a, cudaStream_t s);
 void launch_render_backward(const BwdRenderArgs& a, cudaStream_t s);
 void launch_preprocess_backward(const BwdPreArgs& a, cudaStream_t s);

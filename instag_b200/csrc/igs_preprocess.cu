@@ -110,13 +110,17 @@ template <bool USE_SH>
 __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   __shared__ uint32_t s_warp_sum[PRE_THREADS / 32];
-  __shared__ uint32_t s_excl;
+  __shared__ uint32_t s_excl, s_bid, s_last;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid < 16) { s_view[tid] = __ldg(a.viewmatrix + tid); s_proj[tid] = __ldg(a.projmatrix + tid); }
   if (tid < 3) s_cam[tid] = __ldg(a.campos + tid);
+  // the chunk a CTA works on is handed out in START order, so the CTA a look-back waits
+  // for is always already running (no assumption about the hardware's CTA dispatch order)
+  if (tid == 0) s_bid = atomicAdd(&a.header->ticket, 1u);
   __syncthreads();
+  const int bid = (int)s_bid;
 
-  const int idx = blockIdx.x * PRE_THREADS + tid;
+  const int idx = bid * PRE_THREADS + tid;
   uint32_t tiles = 0;
   int radius = 0;
   if (idx < a.P) {
@@ -156,6 +160,9 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
         if (n_tiles != 0) {
           tiles = n_tiles;
           radius = (int)my_radius;
+          // instances per tile: sizes the tile segments the duplicate kernel fills
+          for (int ty = y0; ty < y1; ty++)
+            for (int tx = x0; tx < x1; tx++) atomicAdd(a.tile_count + ty * a.grid_x + tx, 1u);
           // normal: rotated axis of the smallest RAW scale, flipped to face the camera
           float nx, ny, nz;
           if (a.norm3Ds_precomp) {
@@ -215,10 +222,10 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
     }
     const uint32_t total = __shfl_sync(0xffffffffu, wi, PRE_THREADS / 32 - 1);
     if (lane < PRE_THREADS / 32) s_warp_sum[lane] = wi - w; // exclusive warp offsets
-    const uint32_t excl = lookback_exclusive(a.scan_state, blockIdx.x, total);
+    const uint32_t excl = lookback_exclusive(a.scan_state, bid, total);
     if (lane == 0) {
       s_excl = excl;
-      if (blockIdx.x == gridDim.x - 1) {
+      if (bid == (int)gridDim.x - 1) {
         a.header->num_rendered = excl + total;
         a.header->overflow = (int64_t)(excl + total) > a.capacity ? 1u : 0u;
       }
@@ -226,6 +233,38 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
   }
   __syncthreads();
   if (idx < a.P) a.point_offsets[idx] = s_excl + s_warp_sum[warp] + incl;
+
+  // ---- the CTA that finishes last turns the tile counts into tile ranges ------------------
+  // (reference identifyTileRanges, rasterizer_impl.cu:116-138 + the memset at :313: the
+  // range of a tile is [exclusive prefix of the counts, +count), (0,0) for an empty tile)
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) s_last = atomicAdd(&a.header->done, 1u) == gridDim.x - 1 ? 1u : 0u;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const int T = a.grid_x * a.grid_y;
+  const int per = (T + PRE_THREADS - 1) / PRE_THREADS;
+  const int t0 = tid * per, t1 = min(T, t0 + per);
+  uint32_t sum = 0;
+  for (int t = t0; t < t1; t++) sum += __ldcg(a.tile_count + t);
+  uint32_t inc = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += n;
+  }
+  __syncthreads(); // s_warp_sum is reused
+  if (lane == 31) s_warp_sum[warp] = inc;
+  __syncthreads();
+  uint32_t run = inc - sum;
+  for (int w = 0; w < warp; w++) run += s_warp_sum[w];
+  for (int t = t0; t < t1; t++) {
+    const uint32_t c = __ldcg(a.tile_count + t);
+    a.tile_cursor[t] = run;
+    a.ranges[t] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
+    run += c;
+  }
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,

@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(RT) render_kernel(RenderArgs a) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int unit = blockIdx.x * RW + warp;          // (tile, 8x4 block)
   const int tile = unit >> 3, wb = unit & 7;
-  if (tile >= a.grid_x * a.grid_y) return;
+  if (tile >= a.grid_x * a.grid_y || a.header->overflow) return;
   const int tx = tile % a.grid_x, ty = tile / a.grid_x;
   const int bx = tx * TILE + (wb & 1) * 8, by = ty * TILE + (wb >> 1) * 4;
   const int px = bx + (lane & 7), py = by + (lane >> 3);

@@ -117,7 +117,7 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
     img = torch.empty(lib.igs_img_bytes(W, H), **u8)
     binb = torch.empty(lib.igs_bin_bytes(capacity), **u8)
     sort = sc.buf("sort", lib.igs_sort_bytes(capacity))
-    ctrl = sc.buf("ctrl", lib.igs_ctrl_bytes(P, capacity))
+    ctrl = sc.buf("ctrl", lib.igs_ctrl_bytes(P, W, H))
 
     keep = [_f32c(bg), _f32c(viewmatrix), _f32c(projmatrix), _f32c(campos), _f32c(means3D), _f32c(sh),
             _f32c(colors_precomp), _f32c(opacities), _f32c(scales), _f32c(rotations),
@@ -143,8 +143,7 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
             capacity = int(n.value * 1.1) + 4096
             binb = torch.empty(lib.igs_bin_bytes(capacity), **u8)
             sort = sc.buf("sort", lib.igs_sort_bytes(capacity))
-            ctrl = sc.buf("ctrl", lib.igs_ctrl_bytes(P, capacity))
-            a.bin, a.sort, a.ctrl, a.capacity = binb.data_ptr(), sort.data_ptr(), ctrl.data_ptr(), capacity
+            a.bin, a.sort, a.capacity = binb.data_ptr(), sort.data_ptr(), capacity
             st = lib.igs_forward_bin_render(C.byref(a), stream)
         N.check(st, "forward")
     num_rendered = int(n.value)

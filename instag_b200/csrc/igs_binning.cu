@@ -27,24 +27,16 @@
 
 namespace igs {
 
-constexpr int DUP_THREADS = 256;
+constexpr int DUP_THREADS = PRE_THREADS;
 
 // One warp per 32 Gaussians; the warp's instances are spread evenly over the lanes
 // (a lane finds the Gaussian that owns instance k by a 5-step search over the warp's
 // inclusive counts), so a screen-filling Gaussian does not serialise a thread.
-__global__ void __launch_bounds__(DUP_THREADS) duplicate_kernel(BinArgs a) {
+// f(tile, word) is called once per instance.
+template <class F>
+__device__ __forceinline__ void for_each_instance(uint32_t n, uint32_t xy, uint32_t w, uint32_t depth, int gbase,
+                                                  int grid_x, F&& f) {
   const int lane = threadIdx.x & 31;
-  const int g = (blockIdx.x * DUP_THREADS + threadIdx.x);
-  uint32_t n = 0, xy = 0, w = 1, depth = 0;
-  if (g < a.P) n = __ldg(a.tiles_touched + g);
-  if (n) {
-    const float4 r1 = __ldg(a.splat + (size_t)g * SPLAT_F4 + 1); // x, y, depth, extra0
-    int x0, y0, x1, y1;
-    tile_rect(r1.x, r1.y, __ldg(a.radii + g), a.grid_x, a.grid_y, x0, y0, x1, y1);
-    xy = (uint32_t)x0 | ((uint32_t)y0 << 16);
-    w = (uint32_t)(x1 - x0);
-    depth = __float_as_uint(r1.z);
-  }
   uint32_t incl = n;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -53,7 +45,6 @@ __global__ void __launch_bounds__(DUP_THREADS) duplicate_kernel(BinArgs a) {
   }
   const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
   const uint32_t excl = incl - n;
-  const int gbase = g - lane;
   for (uint32_t kb = 0; kb < total; kb += 32) {
     const uint32_t k = kb + lane;
     // owner = number of lanes whose inclusive count is <= k
@@ -71,11 +62,54 @@ __global__ void __launch_bounds__(DUP_THREADS) duplicate_kernel(BinArgs a) {
     if (k < total) {
       const uint32_t local = k - o_excl;
       const uint32_t row = local / o_w, col = local - row * o_w;
-      const uint32_t t = ((o_xy >> 16) + row) * (uint32_t)a.grid_x + (o_xy & 0xffffu) + col;
-      const uint32_t slot = atomicAdd(a.tile_cursor + t, 1u);
-      if ((int64_t)slot < a.capacity)
-        a.pairs[slot] = ((unsigned long long)o_depth << 32) | (uint32_t)(gbase + o);
+      const uint32_t t = ((o_xy >> 16) + row) * (uint32_t)grid_x + (o_xy & 0xffffu) + col;
+      f(t, ((unsigned long long)o_depth << 32) | (uint32_t)(gbase + o));
     }
+  }
+}
+
+// HIST_SMEM: the CTA first counts its instances per tile in shared memory, reserves one
+// contiguous run of slots per non-empty tile with a single global atomic, and then hands
+// the slots out with shared-memory atomics -- N/(instances a CTA has per tile) global
+// atomics instead of N.  (The order inside a tile segment is irrelevant: tile_sort_kernel
+// sorts it by unique words.)
+template <bool HIST_SMEM>
+__global__ void __launch_bounds__(DUP_THREADS) duplicate_kernel(BinArgs a) {
+  extern __shared__ uint32_t s_slot[];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int g = blockIdx.x * DUP_THREADS + tid;
+  if (HIST_SMEM)
+    for (int t = tid; t < a.num_tiles; t += DUP_THREADS) s_slot[t] = 0u;
+  uint32_t n = 0, xy = 0, w = 1, depth = 0;
+  if (g < a.P) n = __ldg(a.tiles_touched + g);
+  if (n) {
+    const float4 r1 = __ldg(a.splat + (size_t)g * SPLAT_F4 + 1); // x, y, depth, extra0
+    int x0, y0, x1, y1;
+    tile_rect(r1.x, r1.y, __ldg(a.radii + g), a.grid_x, a.grid_y, x0, y0, x1, y1);
+    xy = (uint32_t)x0 | ((uint32_t)y0 << 16);
+    w = (uint32_t)(x1 - x0);
+    depth = __float_as_uint(r1.z);
+  }
+  const int gbase = g - lane;
+  if (HIST_SMEM) {
+    __syncthreads();
+    for_each_instance(n, xy, w, depth, gbase, a.grid_x,
+                      [&](uint32_t t, unsigned long long) { atomicAdd(&s_slot[t], 1u); });
+    __syncthreads();
+    for (int t = tid; t < a.num_tiles; t += DUP_THREADS) {
+      const uint32_t c = s_slot[t];
+      if (c) s_slot[t] = atomicAdd(a.tile_cursor + (size_t)t * CNT_STRIDE, c);
+    }
+    __syncthreads();
+    for_each_instance(n, xy, w, depth, gbase, a.grid_x, [&](uint32_t t, unsigned long long word) {
+      const uint32_t slot = atomicAdd(&s_slot[t], 1u);
+      if ((int64_t)slot < a.capacity) a.pairs[slot] = word;
+    });
+  } else {
+    for_each_instance(n, xy, w, depth, gbase, a.grid_x, [&](uint32_t t, unsigned long long word) {
+      const uint32_t slot = atomicAdd(a.tile_cursor + (size_t)t * CNT_STRIDE, 1u);
+      if ((int64_t)slot < a.capacity) a.pairs[slot] = word;
+    });
   }
 }
 
@@ -84,7 +118,7 @@ __global__ void reset_cursors_kernel(BinArgs a) {
   if (t >= a.num_tiles) return;
   // start of the segment = exclusive prefix of the counts; recomputed from the ranges of the
   // non-empty tiles is not possible for empty ones, but those never receive an instance
-  a.tile_cursor[t] = a.ranges[t].x;
+  a.tile_cursor[(size_t)t * CNT_STRIDE] = a.ranges[t].x;
 }
 
 // ---- per-tile sort --------------------------------------------------------------------
@@ -211,7 +245,11 @@ __global__ void __launch_bounds__(TS_THREADS) tile_sort_kernel(BinArgs a) {
 
 void launch_binning(const BinArgs& a, cudaStream_t s) {
   if (a.P <= 0 || a.num_tiles <= 0) return;
-  duplicate_kernel<<<(a.P + DUP_THREADS - 1) / DUP_THREADS, DUP_THREADS, 0, s>>>(a);
+  const int dup_blocks = (a.P + DUP_THREADS - 1) / DUP_THREADS;
+  if (a.num_tiles <= HIST_SMEM_MAX_TILES)
+    duplicate_kernel<true><<<dup_blocks, DUP_THREADS, (size_t)a.num_tiles * sizeof(uint32_t), s>>>(a);
+  else
+    duplicate_kernel<false><<<dup_blocks, DUP_THREADS, 0, s>>>(a);
   prof_mark(2, s);
   tile_sort_kernel<<<a.num_tiles, TS_THREADS, 0, s>>>(a);
   prof_mark(3, s);

@@ -73,7 +73,11 @@ struct SortLayout { // unsorted (depth|id) pairs grouped by tile, scratch
   }
 };
 
-constexpr int PRE_THREADS = 256;
+constexpr int PRE_THREADS = 512;   // Gaussians per preprocess / duplicate CTA
+// Per-tile counters and cursors live one per 128-byte line: the L2 atomic units then work on
+// ~T different lines instead of T/32 (measured: contended REDs to neighbouring words serialise).
+constexpr int CNT_STRIDE = 32;     // in uint32 words
+constexpr int HIST_SMEM_MAX_TILES = 11264; // CTA-local tile histogram fits 44 KB of shared memory
 
 struct CtrlHeader {
   uint32_t num_rendered;  // written by the preprocess CTA that owns the last Gaussians
@@ -91,8 +95,8 @@ struct CtrlLayout {
     const size_t T = (size_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
     header = o;       o = align_up(o + sizeof(CtrlHeader));
     scan_state = o;   o = align_up(o + (size_t)(pre_blocks ? pre_blocks : 1) * sizeof(unsigned long long));
-    tile_count = o;   o = align_up(o + (T ? T : 1) * sizeof(uint32_t));
-    tile_cursor = o;  o = align_up(o + (T ? T : 1) * sizeof(uint32_t));
+    tile_count = o;   o = align_up(o + (T ? T : 1) * CNT_STRIDE * sizeof(uint32_t));
+    tile_cursor = o;  o = align_up(o + (T ? T : 1) * CNT_STRIDE * sizeof(uint32_t));
     total = o;
   }
   // everything before tile_cursor is zeroed at the start of a frame

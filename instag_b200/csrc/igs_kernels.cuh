@@ -18,8 +18,8 @@ struct PreArgs {
   uint8_t* clamped;
   unsigned long long* scan_state;
   CtrlHeader* header;
-  uint32_t* tile_count;   // [T] instances per tile (atomics), zeroed by the caller
-  uint32_t* tile_cursor;  // [T] next free slot of each tile segment (written by the last CTA)
+  uint32_t* tile_count;   // [T*CNT_STRIDE] instances per tile (atomics), zeroed by the caller
+  uint32_t* tile_cursor;  // [T*CNT_STRIDE] next free slot of each tile segment (written by the last CTA)
   uint2* ranges;          // [T] [start, end) of each tile in the sorted list, (0,0) if empty
 };
 
@@ -30,7 +30,7 @@ struct BinArgs {
   const float4* splat;
   const uint32_t* tiles_touched;
   CtrlHeader* header;
-  uint32_t* tile_cursor;      // [T]
+  uint32_t* tile_cursor;      // [T*CNT_STRIDE]
   const uint2* ranges;        // [T]
   unsigned long long* pairs;  // [capacity] (depth bits << 32 | gaussian id), grouped by tile, unordered inside
   uint32_t* point_list;       // [capacity] sorted

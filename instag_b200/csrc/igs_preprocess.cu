@@ -106,12 +106,18 @@ __device__ __forceinline__ uint32_t lookback_exclusive(unsigned long long* state
   return excl;
 }
 
-template <bool USE_SH>
+template <bool USE_SH, bool HIST_SMEM>
 __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   __shared__ uint32_t s_warp_sum[PRE_THREADS / 32];
   __shared__ uint32_t s_excl, s_bid, s_last;
+  // CTA-local histogram of the instances per tile (HIST_SMEM: the launch gave us 4*T bytes):
+  // one global RED per (CTA, non-empty tile) instead of one per instance
+  extern __shared__ uint32_t s_hist[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int T = a.grid_x * a.grid_y;
+  if (HIST_SMEM)
+    for (int t = tid; t < T; t += PRE_THREADS) s_hist[t] = 0u;
   if (tid < 16) { s_view[tid] = __ldg(a.viewmatrix + tid); s_proj[tid] = __ldg(a.projmatrix + tid); }
   if (tid < 3) s_cam[tid] = __ldg(a.campos + tid);
   // the chunk a CTA works on is handed out in START order, so the CTA a look-back waits
@@ -162,7 +168,10 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
           radius = (int)my_radius;
           // instances per tile: sizes the tile segments the duplicate kernel fills
           for (int ty = y0; ty < y1; ty++)
-            for (int tx = x0; tx < x1; tx++) atomicAdd(a.tile_count + ty * a.grid_x + tx, 1u);
+            for (int tx = x0; tx < x1; tx++) {
+              if (HIST_SMEM) atomicAdd(&s_hist[ty * a.grid_x + tx], 1u);
+              else atomicAdd(a.tile_count + (size_t)(ty * a.grid_x + tx) * CNT_STRIDE, 1u);
+            }
           // normal: rotated axis of the smallest RAW scale, flipped to face the camera
           float nx, ny, nz;
           if (a.norm3Ds_precomp) {
@@ -233,6 +242,12 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
   }
   __syncthreads();
   if (idx < a.P) a.point_offsets[idx] = s_excl + s_warp_sum[warp] + incl;
+  if (HIST_SMEM) { // (the barrier above ordered every thread's shared-memory atomics)
+    for (int t = tid; t < T; t += PRE_THREADS) {
+      const uint32_t c = s_hist[t];
+      if (c) atomicAdd(a.tile_count + (size_t)t * CNT_STRIDE, c);
+    }
+  }
 
   // ---- the CTA that finishes last turns the tile counts into tile ranges ------------------
   // (reference identifyTileRanges, rasterizer_impl.cu:116-138 + the memset at :313: the
@@ -243,11 +258,10 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  const int T = a.grid_x * a.grid_y;
   const int per = (T + PRE_THREADS - 1) / PRE_THREADS;
   const int t0 = tid * per, t1 = min(T, t0 + per);
   uint32_t sum = 0;
-  for (int t = t0; t < t1; t++) sum += __ldcg(a.tile_count + t);
+  for (int t = t0; t < t1; t++) sum += __ldcg(a.tile_count + (size_t)t * CNT_STRIDE);
   uint32_t inc = sum;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -260,8 +274,8 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
   uint32_t run = inc - sum;
   for (int w = 0; w < warp; w++) run += s_warp_sum[w];
   for (int t = t0; t < t1; t++) {
-    const uint32_t c = __ldcg(a.tile_count + t);
-    a.tile_cursor[t] = run;
+    const uint32_t c = __ldcg(a.tile_count + (size_t)t * CNT_STRIDE);
+    a.tile_cursor[(size_t)t * CNT_STRIDE] = run;
     a.ranges[t] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
     run += c;
   }
@@ -281,8 +295,15 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, co
 void launch_preprocess(const PreArgs& a, cudaStream_t s) {
   if (a.P <= 0) return;
   const int blocks = (a.P + PRE_THREADS - 1) / PRE_THREADS;
-  if (a.shs) preprocess_kernel<true><<<blocks, PRE_THREADS, 0, s>>>(a);
-  else preprocess_kernel<false><<<blocks, PRE_THREADS, 0, s>>>(a);
+  const int T = a.grid_x * a.grid_y;
+  const size_t hist = (size_t)T * sizeof(uint32_t);
+  if (T <= HIST_SMEM_MAX_TILES) {
+    if (a.shs) preprocess_kernel<true, true><<<blocks, PRE_THREADS, hist, s>>>(a);
+    else preprocess_kernel<false, true><<<blocks, PRE_THREADS, hist, s>>>(a);
+  } else { // images beyond ~1700x1700: count straight into global memory
+    if (a.shs) preprocess_kernel<true, false><<<blocks, PRE_THREADS, 0, s>>>(a);
+    else preprocess_kernel<false, false><<<blocks, PRE_THREADS, 0, s>>>(a);
+  }
   count_launch();
 }
 

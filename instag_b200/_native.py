@@ -71,6 +71,7 @@ SYMBOLS = {
     "igs_profile_enable": (C.c_int, [C.c_int]),
     "igs_profile_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
     "igs_launch_count": (C.c_uint64, []),
+    "igs_debug_trace": (C.c_int, [_p]),
     "igs_mark_visible": (C.c_int, [C.c_int32, _p, _p, _p, _p, _p]),
 }
 

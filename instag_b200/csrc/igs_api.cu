@@ -120,6 +120,7 @@ static PreArgs make_pre(const IgsFwdArgs* a) {
   p.tile_count = (uint32_t*)(c + cl.tile_count);
   p.tile_cursor = (uint32_t*)(c + cl.tile_cursor);
   p.ranges = (uint2*)((char*)a->img + ImgLayout(a->W, a->H).ranges);
+  p.tile_order = (uint32_t*)((char*)a->img + ImgLayout(a->W, a->H).tile_order);
   return p;
 }
 
@@ -160,6 +161,7 @@ static int run_bin_render(const IgsFwdArgs* a, cudaStream_t s) {
   ra.W = a->W; ra.H = a->H; ra.ED = a->ED; ra.grid_x = ba.grid_x; ra.grid_y = ba.grid_y;
   ra.header = ba.header;
   ra.ranges = ba.ranges;
+  ra.tile_order = (const uint32_t*)(im + il.tile_order);
   ra.point_list = ba.point_list;
   ra.splat = ba.splat;
   ra.extra_attrs = a->extra_attrs;
@@ -249,6 +251,7 @@ int igs_forward_bin_render(const IgsFwdArgs* a, igs_stream_t stream) {
   // still valid), bigger bin / sort: clear the overflow flag, rewind the tile cursors
   const BinArgs ba = make_bin(a);
   if (int r = check_cuda(cudaMemsetAsync(&ba.header->overflow, 0, sizeof(uint32_t), s), "clear overflow")) return r;
+  if (int r = check_cuda(cudaMemsetAsync(&ba.header->render_ticket, 0, sizeof(uint32_t), s), "clear ticket")) return r;
   launch_reset_cursors(ba, s);
   return run_bin_render(a, s);
 }
@@ -271,6 +274,7 @@ int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
   ra.W = a->W; ra.H = a->H; ra.ED = a->ED;
   ra.grid_x = (a->W + TILE - 1) / TILE; ra.grid_y = (a->H + TILE - 1) / TILE;
   ra.ranges = (const uint2*)(im + il.ranges);
+  ra.tile_order = (const uint32_t*)(im + il.tile_order);
   ra.point_list = (const uint32_t*)(b + 0); // point_list is the first array of the bin workspace for any capacity
   (void)bl;
   ra.splat = (const float4*)(g + gl.splat);
@@ -279,6 +283,7 @@ int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
   ra.dL_dcolor = a->dL_dcolor; ra.dL_ddepth = a->dL_ddepth; ra.dL_dnorm = a->dL_dnorm;
   ra.dL_dalpha = a->dL_dalpha; ra.dL_dextra = a->dL_dextra;
   ra.accum = (float*)a->accum;
+  ra.ticket = (uint32_t*)((char*)a->accum + accum_ticket_offset(a->P, a->ED));
   ra.accum_extra = a->ED > 1 ? (float*)((char*)a->accum + align_up((size_t)a->P * ACC_F * sizeof(float))) : nullptr;
   prof_mark(6, s);
   if (a->num_rendered > 0) launch_render_backward(ra, s);
@@ -340,6 +345,10 @@ int igs_profile_read(float* ms, int32_t* frames) {
 }
 
 uint64_t igs_launch_count(void) { return g_launches; }
+
+int igs_debug_trace(void* device_buffer) {
+  return check_cuda(set_render_trace((unsigned long long*)device_buffer), "set trace buffer");
+}
 
 int igs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, igs_stream_t stream) {

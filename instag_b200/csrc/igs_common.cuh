@@ -44,11 +44,12 @@ struct GeomLayout {
 };
 
 struct ImgLayout {
-  size_t ranges, n_contrib, total;
+  size_t ranges, n_contrib, tile_order, total;
   __host__ __device__ ImgLayout(int W, int H) {
     size_t T = (size_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
     size_t o = 0;
     ranges = o;     o = align_up(o + (T ? T : 1) * sizeof(uint2));
+    tile_order = o; o = align_up(o + (T ? T : 1) * sizeof(uint32_t)); // tiles, longest list first
     n_contrib = o;  o = align_up(o + (size_t)(W * H > 0 ? W * H : 1) * sizeof(uint32_t));
     total = o;
   }
@@ -84,7 +85,8 @@ struct CtrlHeader {
   uint32_t overflow;      // num_rendered > capacity
   uint32_t ticket;        // dynamic CTA ids of the preprocess kernel (scan order = start order)
   uint32_t done;          // preprocess CTAs that have finished; the last one scans the tile counts
-  uint32_t pad[4];
+  uint32_t render_ticket; // next (tile, 8x4 block) unit of the persistent render kernel
+  uint32_t pad[3];
 };
 
 struct CtrlLayout {
@@ -103,11 +105,13 @@ struct CtrlLayout {
   __host__ __device__ size_t zeroed() const { return tile_cursor; }
 };
 
-inline size_t accum_bytes(int P, int ED) {
+// [P][16] accumulators | [P][ED-1] side array | unit ticket of the persistent backward kernel
+inline size_t accum_ticket_offset(int P, int ED) {
   size_t p = (size_t)(P > 0 ? P : 1);
   size_t extra = ED > 1 ? (size_t)(ED - 1) : 0; // channels 1.. live in a side array
   return align_up(p * ACC_F * sizeof(float)) + align_up(p * extra * sizeof(float));
 }
+inline size_t accum_bytes(int P, int ED) { return accum_ticket_offset(P, ED) + 256; }
 
 // reference rasterizer_impl.cu:35-50 getHigherMsb: number of tile-id bits sorted
 inline int higher_msb(uint32_t n) {

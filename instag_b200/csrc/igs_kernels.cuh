@@ -21,6 +21,7 @@ struct PreArgs {
   uint32_t* tile_count;   // [T*CNT_STRIDE] instances per tile (atomics), zeroed by the caller
   uint32_t* tile_cursor;  // [T*CNT_STRIDE] next free slot of each tile segment (written by the last CTA)
   uint2* ranges;          // [T] [start, end) of each tile in the sorted list, (0,0) if empty
+  uint32_t* tile_order;   // [T] tile ids, longest list first (the render kernels' launch order)
 };
 
 struct BinArgs {
@@ -39,8 +40,9 @@ struct BinArgs {
 
 struct RenderArgs {
   int W, H, ED, grid_x, grid_y;
-  const CtrlHeader* header; // overflow flag: the tile lists are incomplete, render nothing
+  CtrlHeader* header; // overflow flag: the tile lists are incomplete, render nothing; unit ticket
   const uint2* ranges;
+  const uint32_t* tile_order;
   const uint32_t* point_list;
   const float4* splat;
   const float* extra_attrs; // [P,ED], used for channels >= 1
@@ -52,6 +54,7 @@ struct RenderArgs {
 struct BwdRenderArgs {
   int W, H, ED, grid_x, grid_y;
   const uint2* ranges;
+  const uint32_t* tile_order;
   const uint32_t* point_list;
   const float4* splat;
   const float* extra_attrs;
@@ -59,6 +62,7 @@ struct BwdRenderArgs {
   const float* out_alpha;
   const uint32_t* n_contrib;
   const float *dL_dcolor, *dL_ddepth, *dL_dnorm, *dL_dalpha, *dL_dextra;
+  uint32_t* ticket;   // unit counter, zeroed with the accumulators
   float* accum;       // [P][16]
   float* accum_extra; // [P][ED-1] or NULL
 };
@@ -76,6 +80,10 @@ struct BwdPreArgs {
   float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dnorm3D, *dL_dsh;
   float *dL_dscales, *dL_drotations, *dL_dextra_attrs;
 };
+
+// debug hook (igs_debug_trace): when non-null, the render kernels record per unit
+// {globaltimer at start, at end, smid | unit << 32} -- 3 words per unit, forward units first
+cudaError_t set_render_trace(unsigned long long* device_buffer);
 
 void launch_preprocess(const PreArgs& a, cudaStream_t s);
 void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s);

@@ -63,6 +63,7 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float* __restrict__ s
 // ---- single-pass inclusive scan state (decoupled look-back) ----------------
 // 64-bit word per CTA: high 32 bits = flag (0 empty, 1 aggregate, 2 inclusive
 // prefix), low 32 bits = value.  One 64-bit store/load keeps them consistent.
+constexpr int ORDER_BUCKETS = 2 * PRE_THREADS;
 constexpr unsigned long long FLAG_AGG = 1ull << 32, FLAG_PREFIX = 2ull << 32;
 
 __device__ __forceinline__ unsigned long long ld_state(const unsigned long long* p) {
@@ -273,12 +274,49 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
   __syncthreads();
   uint32_t run = inc - sum;
   for (int w = 0; w < warp; w++) run += s_warp_sum[w];
+  uint32_t cmax = 0;
   for (int t = t0; t < t1; t++) {
     const uint32_t c = __ldcg(a.tile_count + (size_t)t * CNT_STRIDE);
     a.tile_cursor[(size_t)t * CNT_STRIDE] = run;
     a.ranges[t] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
     run += c;
+    cmax = max(cmax, c);
   }
+  // ---- launch order of the render kernels: tiles with the longest lists first (their warps
+  // are the critical path), by one counting pass over ORDER_BUCKETS count classes ----
+  __shared__ uint32_t s_bucket[ORDER_BUCKETS];
+  __shared__ uint32_t s_max[PRE_THREADS / 32];
+  cmax = __reduce_max_sync(0xffffffffu, cmax);
+  if (lane == 0) s_max[warp] = cmax;
+  for (int b = tid; b < ORDER_BUCKETS; b += PRE_THREADS) s_bucket[b] = 0u;
+  __syncthreads();
+#pragma unroll
+  for (int w = 0; w < PRE_THREADS / 32; w++) cmax = max(cmax, s_max[w]);
+  const float qs = (float)(ORDER_BUCKETS - 1) / (float)max(cmax, 1u);
+#define ORDER_BUCKET(c) ((ORDER_BUCKETS - 1) - min(ORDER_BUCKETS - 1, (int)((float)(c) * qs)))
+  for (int t = t0; t < t1; t++) atomicAdd(&s_bucket[ORDER_BUCKET(__ldcg(a.tile_count + (size_t)t * CNT_STRIDE))], 1u);
+  __syncthreads();
+  { // exclusive scan of the bucket sizes (ORDER_BUCKETS == 2 * PRE_THREADS: two per thread)
+    const uint32_t c0 = s_bucket[2 * tid], c1 = s_bucket[2 * tid + 1];
+    uint32_t in2 = c0 + c1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t n = __shfl_up_sync(0xffffffffu, in2, o);
+      if (lane >= o) in2 += n;
+    }
+    if (lane == 31) s_max[warp] = in2;
+    __syncthreads();
+    uint32_t base = in2 - (c0 + c1);
+    for (int w = 0; w < warp; w++) base += s_max[w];
+    s_bucket[2 * tid] = base;
+    s_bucket[2 * tid + 1] = base + c0;
+  }
+  __syncthreads();
+  for (int t = t0; t < t1; t++) {
+    const uint32_t slot = atomicAdd(&s_bucket[ORDER_BUCKET(__ldcg(a.tile_count + (size_t)t * CNT_STRIDE))], 1u);
+    a.tile_order[slot] = (uint32_t)t;
+  }
+#undef ORDER_BUCKET
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,

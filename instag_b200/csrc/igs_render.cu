@@ -23,13 +23,27 @@
 //
 // Bound: FP32 issue.  Per evaluated pair ~15 flop + 1 MUFU.EX2, per blended
 // pair +17 flop.  DRAM floor: 64 B per instance + 40 B per pixel.
+#include <cstdlib>
 #include "igs_common.cuh"
 #include "igs_kernels.cuh"
 
 namespace igs {
 
-constexpr int RW = 2;           // warps (8x4 pixel blocks) per CTA
+static __device__ unsigned long long* g_trace = nullptr;
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ uint32_t smid() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %smid;" : "=r"(r));
+  return r;
+}
+
+constexpr int RW = 4;           // warps per CTA: one per SM sub-partition
 constexpr int RT = RW * 32;     // threads per CTA
+constexpr int RG = 4;           // survivors composited per trip of the inner loop
 
 __device__ __forceinline__ float4 lds128(uint32_t addr) {
   float4 v;
@@ -40,6 +54,9 @@ __device__ __forceinline__ void sts128(uint32_t addr, float4 v) {
   asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
+// Persistent kernel: every SM holds as many 4-warp CTAs as fit, and every WARP pulls (tile,
+// 8x4 block) units from one global ticket, heaviest tiles first (tile_order), until the
+// frame is done -- the four sub-partitions of an SM stay evenly loaded to the end.
 template <int ED_T> // 0, 1, or -1 = generic (runtime ED up to IGS_MAX_EXTRA_DIMS)
 __global__ void __launch_bounds__(RT) render_kernel(RenderArgs a) {
   // per warp: 4 planes of 32 float4 (r0..r3 of the chunk's survivors) = 2 KB
@@ -47,9 +64,26 @@ __global__ void __launch_bounds__(RT) render_kernel(RenderArgs a) {
   __shared__ uint32_t s_id[ED_T < 0 ? RW : 1][32];
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int unit = blockIdx.x * RW + warp;          // (tile, 8x4 block)
-  const int tile = unit >> 3, wb = unit & 7;
-  if (tile >= a.grid_x * a.grid_y || a.header->overflow) return;
+  if (a.header->overflow) return;
+  const int num_units = a.grid_x * a.grid_y * 8;
+  const int ED = ED_T < 0 ? a.ED : ED_T;
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(&s_rec[warp][0][0]);
+  const uint32_t smine = sbase + lane * 16;         // my slot in plane 0; planes are 512 B apart
+  const float bg0 = __ldg(a.bg + 0), bg1 = __ldg(a.bg + 1), bg2 = __ldg(a.bg + 2);
+
+ for (;;) {
+  int unit = 0;
+  if (lane == 0) unit = (int)atomicAdd(&a.header->render_ticket, 1u);
+  unit = __shfl_sync(0xffffffffu, unit, 0);
+  if (unit >= num_units) break;
+  unsigned long long* const trace = g_trace;
+  const unsigned long long t_start = trace ? gtimer() : 0ull;
+  // consecutive tickets (= the four warps of a CTA, one SM) go to four DIFFERENT tiles, so that
+  // an SM's share of the frame is a sum of independent unit costs (groups of 4 tiles x 8 blocks)
+  const int num_tiles = a.grid_x * a.grid_y;
+  int slot = ((unit >> 5) << 2) + (unit & 3), wb = (unit >> 2) & 7;
+  if (((unit >> 5) << 2) + 4 > num_tiles) { slot = unit >> 3; wb = unit & 7; } // ragged last group
+  const int tile = (int)__ldg(a.tile_order + slot); // longest lists first
   const int tx = tile % a.grid_x, ty = tile / a.grid_x;
   const int bx = tx * TILE + (wb & 1) * 8, by = ty * TILE + (wb >> 1) * 4;
   const int px = bx + (lane & 7), py = by + (lane >> 3);
@@ -58,10 +92,7 @@ __global__ void __launch_bounds__(RT) render_kernel(RenderArgs a) {
   const float wx0 = (float)bx, wx1 = wx0 + 7.f, wy0 = (float)by, wy1 = wy0 + 3.f;
   const uint2 range = __ldg(a.ranges + tile);
   const int total = (int)(range.y - range.x);
-  const int ED = ED_T < 0 ? a.ED : ED_T;
   const uint32_t* __restrict__ list = a.point_list + range.x;
-  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(&s_rec[warp][0][0]);
-  const uint32_t smine = sbase + lane * 16;         // my slot in plane 0; planes are 512 B apart
 
   float T = 1.0f;
   float C0 = 0.f, C1 = 0.f, C2 = 0.f, Dp = 0.f, N0 = 0.f, N1 = 0.f, N2 = 0.f, E0 = 0.f;
@@ -112,48 +143,65 @@ __global__ void __launch_bounds__(RT) render_kernel(RenderArgs a) {
     }
     __syncwarp();
     while (m) {
-      // two survivors per trip: their alpha chains are independent, only the blend is ordered
-      const int ja = __ffs(m) - 1;
-      m &= m - 1;
-      const bool two = m != 0;
-      const int jb = two ? __ffs(m) - 1 : ja;
-      m &= m - 1;
-      const float4 a1 = lds128(sbase + 512 + ja * 16), a0 = lds128(sbase + ja * 16);
-      const float4 b1 = lds128(sbase + 512 + jb * 16), b0 = lds128(sbase + jb * 16);
-      const float dxa = __fsub_rn(a1.x, pxf), dya = __fsub_rn(a1.y, pyf);
-      const float dxb = __fsub_rn(b1.x, pxf), dyb = __fsub_rn(b1.y, pyf);
-      const float pa = gauss_power(a0.x, a0.y, a0.z, dxa, dya);
-      const float pb = gauss_power(b0.x, b0.y, b0.z, dxb, dyb);
-      const float alpha_a = fminf(0.99f, __fmul_rn(a0.w, expf(pa)));
-      const float alpha_b = fminf(0.99f, __fmul_rn(b0.w, expf(pb)));
-      const bool oka = !(pa > 0.0f) && !(alpha_a < ALPHA_MIN);
-      const bool okb = two && !(pb > 0.0f) && !(alpha_b < ALPHA_MIN);
+      // FOUR survivors per trip.  Their alpha chains are independent (instruction-level
+      // parallelism for a warp that is alone on its scheduler at the end of the frame); only the
+      // transmittance recurrence is ordered, and it is written branch-free: a splat that does
+      // not blend gets weight 0 and leaves T alone.
+      int j[RG];
+      bool have[RG];
 #pragma unroll
-      for (int h = 0; h < 2; h++) {
-        const bool ok = h ? okb : oka;
-        if (!ok || done) continue;
-        const float alpha = h ? alpha_b : alpha_a;
-        const int j = h ? jb : ja;
-        const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
-        if (test_T < T_MIN) { done = true; continue; }
-        // X += f*alpha*T  ->  fma(f*alpha, T, X)   (reference forward.cu:425-431)
-        const float4 r1 = h ? b1 : a1;
-        const float4 r2 = lds128(sbase + 1024 + j * 16);
-        const float4 r3 = lds128(sbase + 1536 + j * 16);
-        C0 = __fmaf_rn(__fmul_rn(r2.x, alpha), T, C0);
-        C1 = __fmaf_rn(__fmul_rn(r2.y, alpha), T, C1);
-        C2 = __fmaf_rn(__fmul_rn(r2.z, alpha), T, C2);
-        Dp = __fmaf_rn(__fmul_rn(r1.z, alpha), T, Dp);
-        N0 = __fmaf_rn(__fmul_rn(r2.w, alpha), T, N0);
-        N1 = __fmaf_rn(__fmul_rn(r3.x, alpha), T, N1);
-        N2 = __fmaf_rn(__fmul_rn(r3.y, alpha), T, N2);
-        if (ED_T == 1) E0 = __fmaf_rn(__fmul_rn(r1.w, alpha), T, E0);
+      for (int h = 0; h < RG; h++) {
+        have[h] = m != 0;
+        j[h] = have[h] ? __ffs(m) - 1 : j[h ? h - 1 : 0];
+        m &= m - 1;
+      }
+      float alpha[RG], zd[RG], ze[RG];
+      bool ok[RG];
+#pragma unroll
+      for (int h = 0; h < RG; h++) {
+        const float4 r1 = lds128(sbase + 512 + j[h] * 16), r0 = lds128(sbase + j[h] * 16);
+        const float dx = __fsub_rn(r1.x, pxf), dy = __fsub_rn(r1.y, pyf);
+        const float pw = gauss_power(r0.x, r0.y, r0.z, dx, dy);
+        alpha[h] = fminf(0.99f, __fmul_rn(r0.w, expf(pw)));
+        ok[h] = have[h] && !(pw > 0.0f) && !(alpha[h] < ALPHA_MIN);
+        zd[h] = r1.z; ze[h] = r1.w;
+      }
+      // ordered part: T, done, last contributor (bit-exact with the reference), blend weights
+      float w[RG];
+      bool any = false;
+#pragma unroll
+      for (int h = 0; h < RG; h++) {
+        const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha[h]));
+        const bool live_h = ok[h] && !done;
+        const bool stop = test_T < T_MIN;
+        const bool blend = live_h && !stop;
+        done = done || (live_h && stop);
+        w[h] = blend ? __fmul_rn(alpha[h], T) : 0.f;
+        T = blend ? test_T : T;
+        last_contributor = blend ? (uint32_t)(cb + j[h] + 1) : last_contributor;
+        any = any || blend;
+      }
+      if (!__any_sync(0xffffffffu, any)) continue;
+      // X += f*(alpha*T): one rounding away from the reference's fma(f*alpha, T, X)
+      // (forward.cu:425-431), far inside the 1e-5 image tolerance
+#pragma unroll
+      for (int h = 0; h < RG; h++) {
+        const float4 r2 = lds128(sbase + 1024 + j[h] * 16);
+        const float4 r3 = lds128(sbase + 1536 + j[h] * 16);
+        C0 = __fmaf_rn(r2.x, w[h], C0);
+        C1 = __fmaf_rn(r2.y, w[h], C1);
+        C2 = __fmaf_rn(r2.z, w[h], C2);
+        Dp = __fmaf_rn(zd[h], w[h], Dp);
+        N0 = __fmaf_rn(r2.w, w[h], N0);
+        N1 = __fmaf_rn(r3.x, w[h], N1);
+        N2 = __fmaf_rn(r3.y, w[h], N2);
+        if (ED_T == 1) E0 = __fmaf_rn(ze[h], w[h], E0);
         if (ED_T < 0) {
-          const float* e = a.extra_attrs + (size_t)s_id[warp][j] * ED;
-          for (int c = 0; c < ED; c++) Ex[c] = __fmaf_rn(__fmul_rn(__ldg(e + c), alpha), T, Ex[c]);
+          if (w[h] != 0.f) {
+            const float* e = a.extra_attrs + (size_t)s_id[warp][j[h]] * ED;
+            for (int c = 0; c < ED; c++) Ex[c] = __fmaf_rn(__ldg(e + c), w[h], Ex[c]);
+          }
         }
-        T = test_T;
-        last_contributor = (uint32_t)(cb + j + 1);
       }
     }
   }
@@ -162,9 +210,9 @@ __global__ void __launch_bounds__(RT) render_kernel(RenderArgs a) {
     const size_t HW = (size_t)a.H * a.W, pix = (size_t)py * a.W + px;
     a.out_alpha[pix] = __fsub_rn(1.f, T);
     a.n_contrib[pix] = last_contributor;
-    a.out_color[pix] = __fmaf_rn(T, __ldg(a.bg + 0), C0);
-    a.out_color[HW + pix] = __fmaf_rn(T, __ldg(a.bg + 1), C1);
-    a.out_color[2 * HW + pix] = __fmaf_rn(T, __ldg(a.bg + 2), C2);
+    a.out_color[pix] = __fmaf_rn(T, bg0, C0);
+    a.out_color[HW + pix] = __fmaf_rn(T, bg1, C1);
+    a.out_color[2 * HW + pix] = __fmaf_rn(T, bg2, C2);
     a.out_depth[pix] = Dp;
     a.out_norm[pix] = N0;
     a.out_norm[HW + pix] = N1;
@@ -173,15 +221,39 @@ __global__ void __launch_bounds__(RT) render_kernel(RenderArgs a) {
     if (ED_T < 0)
       for (int c = 0; c < ED; c++) a.out_extra[c * HW + pix] = Ex[c];
   }
+  __syncwarp(); // the next unit reuses this warp's shared-memory slots
+  if (trace && lane == 0) {
+    trace[3 * unit] = t_start; trace[3 * unit + 1] = gtimer();
+    trace[3 * unit + 2] = (unsigned long long)smid() | ((unsigned long long)total << 32);
+  }
+ } // unit loop
 }
+
+// CTAs that fit on the device at once (all SMs), per kernel variant; cached per process
+template <class K>
+static int resident_ctas(K kernel, int threads) {
+  int dev = 0, sms = 0, per_sm = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0);
+  // 6 x 4 warps per SM measured best on B200 (sweep 2..8 in profiles/r01_v3_notes.md): fewer
+  // resident warps leave a deeper ticket queue (better balance), more hide more latency
+  per_sm = min(per_sm, 6);
+  if (const char* e = getenv("IGS_CTAS_PER_SM")) per_sm = max(1, atoi(e)); // experiments only
+  return (sms > 0 ? sms : 148) * (per_sm > 0 ? per_sm : 1);
+}
+
+cudaError_t set_render_trace(unsigned long long* p) { return cudaMemcpyToSymbol(g_trace, &p, sizeof p); }
 
 void launch_render(const RenderArgs& a, cudaStream_t s) {
   if (a.W <= 0 || a.H <= 0) return;
+  static const int cap0 = resident_ctas(render_kernel<0>, RT), cap1 = resident_ctas(render_kernel<1>, RT),
+                   capx = resident_ctas(render_kernel<-1>, RT);
   const int units = a.grid_x * a.grid_y * 8;
-  const int grid = (units + RW - 1) / RW;
-  if (a.ED == 0) render_kernel<0><<<grid, RT, 0, s>>>(a);
-  else if (a.ED == 1) render_kernel<1><<<grid, RT, 0, s>>>(a);
-  else render_kernel<-1><<<grid, RT, 0, s>>>(a);
+  const int want = (units + RW - 1) / RW;
+  if (a.ED == 0) render_kernel<0><<<min(want, cap0), RT, 0, s>>>(a);
+  else if (a.ED == 1) render_kernel<1><<<min(want, cap1), RT, 0, s>>>(a);
+  else render_kernel<-1><<<min(want, capx), RT, 0, s>>>(a);
   count_launch();
 }
 

@@ -15,6 +15,7 @@
 // (splat_may_touch, igs_common.cuh), 32 at a time, and only walks the survivors.
 //
 // Bound: FP32 issue + L2 atomics.  Per blended pair ~110 flop.
+#include <cstdlib>
 #include "igs_common.cuh"
 #include "igs_kernels.cuh"
 
@@ -46,7 +47,7 @@ __device__ __forceinline__ float warp_transpose_reduce16(const float (&v)[16], i
   return w1 + __shfl_xor_sync(FULL, w1, 1);
 }
 
-constexpr int BW = 2;        // warps (8x4 pixel blocks) per CTA
+constexpr int BW = 4;        // warps per CTA: one per SM sub-partition
 constexpr int BT = BW * 32;
 
 __device__ __forceinline__ float4 lds128b(uint32_t addr) {
@@ -78,26 +79,39 @@ __global__ void __launch_bounds__(BT) render_backward_kernel(BwdRenderArgs a) {
   __shared__ uint32_t s_id[BW][32];
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int unit = blockIdx.x * BW + warp;
-  const int tile = unit >> 3, wb = unit & 7;
-  if (tile >= a.grid_x * a.grid_y) return;
+  const int num_units = a.grid_x * a.grid_y * 8;
+  const int ED = ED_T < 0 ? a.ED : ED_T;
+  const size_t HW = (size_t)a.H * a.W;
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(&s_rec[warp][0][0]);
+  const uint32_t smine = sbase + lane * 16;
+  const uint32_t sidb = (uint32_t)__cvta_generic_to_shared(&s_id[warp][0]);
+  const float bg0 = __ldg(a.bg), bg1 = __ldg(a.bg + 1), bg2 = __ldg(a.bg + 2);
+
+ // persistent: every warp pulls (tile, 8x4 block) units from one ticket, heaviest tiles first
+ for (;;) {
+  int unit = 0;
+  if (lane == 0) unit = (int)atomicAdd(a.ticket, 1u);
+  unit = __shfl_sync(0xffffffffu, unit, 0);
+  if (unit >= num_units) break;
+  // consecutive tickets (= the four warps of a CTA, one SM) go to four DIFFERENT tiles, so that
+  // an SM's share of the frame is a sum of independent unit costs (groups of 4 tiles x 8 blocks)
+  const int num_tiles = a.grid_x * a.grid_y;
+  int slot = ((unit >> 5) << 2) + (unit & 3), wb = (unit >> 2) & 7;
+  if (((unit >> 5) << 2) + 4 > num_tiles) { slot = unit >> 3; wb = unit & 7; } // ragged last group
+  const int tile = (int)__ldg(a.tile_order + slot);
   const int tx = tile % a.grid_x, ty = tile / a.grid_x;
   const int bx = tx * TILE + (wb & 1) * 8, by = ty * TILE + (wb >> 1) * 4;
   const int px = bx + (lane & 7), py = by + (lane >> 3);
   const bool inside = px < a.W && py < a.H;
   const float pxf = (float)px, pyf = (float)py;
   const float wx0 = (float)bx, wx1 = wx0 + 7.f, wy0 = (float)by, wy1 = wy0 + 3.f;
-  const size_t HW = (size_t)a.H * a.W, pix = (size_t)py * a.W + px;
+  const size_t pix = (size_t)py * a.W + px;
   const uint2 range = __ldg(a.ranges + tile);
-  const int ED = ED_T < 0 ? a.ED : ED_T;
-  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(&s_rec[warp][0][0]);
-  const uint32_t smine = sbase + lane * 16;
-  const uint32_t sidb = (uint32_t)__cvta_generic_to_shared(&s_id[warp][0]);
 
   const int last_contributor = inside ? (int)a.n_contrib[pix] : 0;
   // nothing behind the last contributor of any of the warp's pixels matters
   const int wmax = (int)__reduce_max_sync(0xffffffffu, (unsigned)last_contributor);
-  if (wmax == 0) return;
+  if (wmax == 0) continue;
   const float T_final = inside ? __fsub_rn(1.f, a.out_alpha[pix]) : 0.f;
   float dpc0 = 0, dpc1 = 0, dpc2 = 0, dpd = 0, dpn0 = 0, dpn1 = 0, dpn2 = 0, dpa = 0, dpe0 = 0;
   if (inside) {
@@ -108,7 +122,7 @@ __global__ void __launch_bounds__(BT) render_backward_kernel(BwdRenderArgs a) {
     if (ED >= 1) dpe0 = a.dL_dextra[pix];
   }
   PixelBack st{T_final, 0.f, 0.f, 0.f};
-  const float bg_dot = __ldg(a.bg) * dpc0 + __ldg(a.bg + 1) * dpc1 + __ldg(a.bg + 2) * dpc2;
+  const float bg_dot = bg0 * dpc0 + bg1 * dpc1 + bg2 * dpc2;
   const float nbgT = -T_final * bg_dot;
 
   // entry e of the reverse walk is list position wmax-1-e (= its `contributor` index)
@@ -207,15 +221,33 @@ __global__ void __launch_bounds__(BT) render_backward_kernel(BwdRenderArgs a) {
       }
     }
   }
+  __syncwarp(); // the next unit reuses this warp's shared-memory slots
+ } // unit loop
+}
+
+template <class K>
+static int resident_ctas_bwd(K kernel, int threads) {
+  int dev = 0, sms = 0, per_sm = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0);
+  // 6 x 4 warps per SM measured best on B200 (sweep 2..8 in profiles/r01_v3_notes.md): fewer
+  // resident warps leave a deeper ticket queue (better balance), more hide more latency
+  per_sm = min(per_sm, 6);
+  if (const char* e = getenv("IGS_CTAS_PER_SM")) per_sm = max(1, atoi(e)); // experiments only
+  return (sms > 0 ? sms : 148) * (per_sm > 0 ? per_sm : 1);
 }
 
 void launch_render_backward(const BwdRenderArgs& a, cudaStream_t s) {
   if (a.W <= 0 || a.H <= 0) return;
+  static const int cap0 = resident_ctas_bwd(render_backward_kernel<0>, BT),
+                   cap1 = resident_ctas_bwd(render_backward_kernel<1>, BT),
+                   capx = resident_ctas_bwd(render_backward_kernel<-1>, BT);
   const int units = a.grid_x * a.grid_y * 8;
-  const int grid = (units + BW - 1) / BW;
-  if (a.ED == 0) render_backward_kernel<0><<<grid, BT, 0, s>>>(a);
-  else if (a.ED == 1) render_backward_kernel<1><<<grid, BT, 0, s>>>(a);
-  else render_backward_kernel<-1><<<grid, BT, 0, s>>>(a);
+  const int want = (units + BW - 1) / BW;
+  if (a.ED == 0) render_backward_kernel<0><<<min(want, cap0), BT, 0, s>>>(a);
+  else if (a.ED == 1) render_backward_kernel<1><<<min(want, cap1), BT, 0, s>>>(a);
+  else render_backward_kernel<-1><<<min(want, capx), BT, 0, s>>>(a);
   count_launch();
 }
 

@@ -58,6 +58,10 @@ typedef struct IgsFwdArgs {
   int32_t W, H;
   float tan_fovx, tan_fovy, scale_modifier;
   int32_t prefiltered, debug;
+  /* != 0: out_norm receives the unit normal n / max(|n|, 1e-12) -- the F.normalize(norm, dim=0) the
+   * reference applies in Python right after the call (DGR diff_gauss/__init__.py:48) -- and |n| is
+   * kept in the img workspace for igs_backward */
+  int32_t normalize_norm;
   /* camera (device) */
   const float* bg;          /* [3] */
   const float* viewmatrix;  /* [16] row-vector convention (transposed W2C) */
@@ -76,7 +80,7 @@ typedef struct IgsFwdArgs {
   /* outputs (device); every element is written, no pre-zeroing needed */
   float* out_color; /* [3,H,W] */
   float* out_depth; /* [1,H,W] */
-  float* out_norm;  /* [3,H,W] un-normalised */
+  float* out_norm;  /* [3,H,W] un-normalised (normalize_norm == 0) or unit length */
   float* out_alpha; /* [1,H,W] */
   float* out_extra; /* [ED,H,W] or NULL */
   int32_t* radii;   /* [P] */
@@ -97,6 +101,9 @@ typedef struct IgsBwdArgs {
   int32_t W, H;
   float tan_fovx, tan_fovy, scale_modifier;
   int32_t debug;
+  /* same value as in the forward call; != 0: dL_dnorm is the gradient w.r.t. the UNIT normal and
+   * out_norm (the forward's normalised output) must be given */
+  int32_t normalize_norm;
   int64_t num_rendered;
   const float* bg;
   const float* viewmatrix;
@@ -116,6 +123,7 @@ typedef struct IgsBwdArgs {
   const void* img;
   const void* bin;
   const float* out_alpha; /* [1,H,W] as returned by forward */
+  const float* out_norm;  /* [3,H,W] as returned by forward; only read when normalize_norm != 0 */
   /* upstream gradients (device, contiguous) */
   const float* dL_dcolor; /* [3,H,W] */
   const float* dL_ddepth; /* [1,H,W] */
@@ -152,7 +160,7 @@ size_t igs_accum_bytes(int32_t P, int32_t ED);
  *            r,g,b,nx | ny,nz,-,-}, tiles_touched u32[P], point_offsets u32[P]
  *            (inclusive scan), clamped u8[P] (bit c = colour channel c clamped)
  * bin   (2): point_list u32[cap], keys u64[cap]      (sorted)
- * img   (2): ranges uint2[T], n_contrib u32[H*W] */
+ * img   (2): ranges uint2[T], n_contrib u32[H*W]  (+ private: tile order, normal lengths) */
 void igs_geom_layout(int32_t P, int64_t* off4);
 void igs_bin_layout(int64_t capacity, int64_t* off2);
 void igs_img_layout(int32_t W, int32_t H, int64_t* off2);

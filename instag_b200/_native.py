@@ -21,7 +21,7 @@ class IgsFwdArgs(C.Structure):
         ("P", C.c_int32), ("D", C.c_int32), ("M", C.c_int32), ("ED", C.c_int32),
         ("W", C.c_int32), ("H", C.c_int32),
         ("tan_fovx", C.c_float), ("tan_fovy", C.c_float), ("scale_modifier", C.c_float),
-        ("prefiltered", C.c_int32), ("debug", C.c_int32),
+        ("prefiltered", C.c_int32), ("debug", C.c_int32), ("normalize_norm", C.c_int32),
         ("bg", _p), ("viewmatrix", _p), ("projmatrix", _p), ("campos", _p),
         ("means3D", _p), ("shs", _p), ("colors_precomp", _p), ("opacities", _p), ("scales", _p),
         ("rotations", _p), ("cov3Ds_precomp", _p), ("norm3Ds_precomp", _p), ("extra_attrs", _p),
@@ -38,12 +38,12 @@ class IgsBwdArgs(C.Structure):
         ("P", C.c_int32), ("D", C.c_int32), ("M", C.c_int32), ("ED", C.c_int32),
         ("W", C.c_int32), ("H", C.c_int32),
         ("tan_fovx", C.c_float), ("tan_fovy", C.c_float), ("scale_modifier", C.c_float),
-        ("debug", C.c_int32),
+        ("debug", C.c_int32), ("normalize_norm", C.c_int32),
         ("num_rendered", C.c_int64),
         ("bg", _p), ("viewmatrix", _p), ("projmatrix", _p), ("campos", _p),
         ("means3D", _p), ("shs", _p), ("colors_precomp", _p), ("scales", _p), ("rotations", _p),
         ("cov3Ds_precomp", _p), ("norm3Ds_precomp", _p), ("extra_attrs", _p), ("radii", _p),
-        ("geom", _p), ("img", _p), ("bin", _p), ("out_alpha", _p),
+        ("geom", _p), ("img", _p), ("bin", _p), ("out_alpha", _p), ("out_norm", _p),
         ("dL_dcolor", _p), ("dL_ddepth", _p), ("dL_dnorm", _p), ("dL_dalpha", _p), ("dL_dextra", _p),
         ("accum", _p),
         ("dL_dmeans2D", _p), ("dL_dcolors", _p), ("dL_dopacity", _p), ("dL_dmeans3D", _p),

@@ -169,6 +169,8 @@ static int run_bin_render(const IgsFwdArgs* a, cudaStream_t s) {
   ra.out_color = a->out_color; ra.out_depth = a->out_depth; ra.out_norm = a->out_norm;
   ra.out_alpha = a->out_alpha; ra.out_extra = a->out_extra;
   ra.n_contrib = (uint32_t*)(im + il.n_contrib);
+  ra.norm_len = (float*)(im + il.norm_len);
+  ra.normalize = a->normalize_norm != 0;
   launch_render(ra, s);
   prof_mark(5, s);
   return stage_check(debug, s, "render");
@@ -261,7 +263,9 @@ int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
   if (a->P < 0 || a->W <= 0 || a->H <= 0 || a->ED < 0 || a->ED > IGS_MAX_EXTRA_DIMS) { set_error("bad sizes"); return IGS_ERR_INVALID; }
   if (a->P == 0) return IGS_OK; // reference rasterize_points.cu:194
   if (!a->accum || !a->geom || !a->img || !a->bin || !a->out_alpha || !a->dL_dcolor || !a->dL_ddepth ||
-      !a->dL_dnorm || !a->dL_dalpha || (a->ED > 0 && !a->dL_dextra)) { set_error("null buffer"); return IGS_ERR_INVALID; }
+      !a->dL_dnorm || !a->dL_dalpha || (a->ED > 0 && !a->dL_dextra) || (a->normalize_norm && !a->out_norm)) {
+    set_error("null buffer"); return IGS_ERR_INVALID;
+  }
   cudaStream_t s = (cudaStream_t)stream;
   const bool debug = a->debug != 0;
   const GeomLayout gl(a->P);
@@ -280,6 +284,9 @@ int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
   ra.splat = (const float4*)(g + gl.splat);
   ra.extra_attrs = a->extra_attrs; ra.bg = a->bg; ra.out_alpha = a->out_alpha;
   ra.n_contrib = (const uint32_t*)(im + il.n_contrib);
+  ra.norm_len = (const float*)(im + il.norm_len);
+  ra.normalize = a->normalize_norm != 0;
+  ra.out_norm = a->out_norm;
   ra.dL_dcolor = a->dL_dcolor; ra.dL_ddepth = a->dL_ddepth; ra.dL_dnorm = a->dL_dnorm;
   ra.dL_dalpha = a->dL_dalpha; ra.dL_dextra = a->dL_dextra;
   ra.accum = (float*)a->accum;

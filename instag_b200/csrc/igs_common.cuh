@@ -44,13 +44,14 @@ struct GeomLayout {
 };
 
 struct ImgLayout {
-  size_t ranges, n_contrib, tile_order, total;
+  size_t ranges, n_contrib, tile_order, norm_len, total;
   __host__ __device__ ImgLayout(int W, int H) {
     size_t T = (size_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
     size_t o = 0;
     ranges = o;     o = align_up(o + (T ? T : 1) * sizeof(uint2));
     tile_order = o; o = align_up(o + (T ? T : 1) * sizeof(uint32_t)); // tiles, longest list first
     n_contrib = o;  o = align_up(o + (size_t)(W * H > 0 ? W * H : 1) * sizeof(uint32_t));
+    norm_len = o;   o = align_up(o + (size_t)(W * H > 0 ? W * H : 1) * sizeof(float)); // |n| per pixel (fused normalize)
     total = o;
   }
 };

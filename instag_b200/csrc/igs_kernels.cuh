@@ -49,6 +49,8 @@ struct RenderArgs {
   const float* bg;
   float *out_color, *out_depth, *out_norm, *out_alpha, *out_extra;
   uint32_t* n_contrib;
+  float* norm_len;   // [H*W] |n| before normalisation, written when normalize != 0
+  int normalize;
 };
 
 struct BwdRenderArgs {
@@ -62,6 +64,9 @@ struct BwdRenderArgs {
   const float* out_alpha;
   const uint32_t* n_contrib;
   const float *dL_dcolor, *dL_ddepth, *dL_dnorm, *dL_dalpha, *dL_dextra;
+  const float* out_norm;  // unit normals of the forward, read when normalize != 0
+  const float* norm_len;  // [H*W]
+  int normalize;
   uint32_t* ticket;   // unit counter, zeroed with the accumulators
   float* accum;       // [P][16]
   float* accum_extra; // [P][ED-1] or NULL

@@ -214,6 +214,12 @@ __global__ void __launch_bounds__(RT) render_kernel(RenderArgs a) {
     a.out_color[HW + pix] = __fmaf_rn(T, bg1, C1);
     a.out_color[2 * HW + pix] = __fmaf_rn(T, bg2, C2);
     a.out_depth[pix] = Dp;
+    if (a.normalize) { // F.normalize(norm, p=2, dim=0): n / max(|n|, 1e-12)  (DGR diff_gauss/__init__.py:48)
+      const float len = __fsqrt_rn(__fmaf_rn(N2, N2, __fmaf_rn(N1, N1, __fmul_rn(N0, N0))));
+      const float den = fmaxf(len, 1e-12f);
+      a.norm_len[pix] = len;
+      N0 = __fdiv_rn(N0, den); N1 = __fdiv_rn(N1, den); N2 = __fdiv_rn(N2, den);
+    }
     a.out_norm[pix] = N0;
     a.out_norm[HW + pix] = N1;
     a.out_norm[2 * HW + pix] = N2;

@@ -118,6 +118,18 @@ __global__ void __launch_bounds__(BT) render_backward_kernel(BwdRenderArgs a) {
     dpc0 = a.dL_dcolor[pix]; dpc1 = a.dL_dcolor[HW + pix]; dpc2 = a.dL_dcolor[2 * HW + pix];
     dpd = a.dL_ddepth[pix];
     dpn0 = a.dL_dnorm[pix]; dpn1 = a.dL_dnorm[HW + pix]; dpn2 = a.dL_dnorm[2 * HW + pix];
+    if (a.normalize) {
+      // backward of n_hat = n / max(|n|, eps): (g - n_hat <n_hat, g>) / |n|, and g / eps where the
+      // clamp is active (what autograd derives for F.normalize, DGR diff_gauss/__init__.py:48)
+      const float len = a.norm_len[pix];
+      if (len > 1e-12f) {
+        const float h0 = a.out_norm[pix], h1 = a.out_norm[HW + pix], h2 = a.out_norm[2 * HW + pix];
+        const float d = h0 * dpn0 + h1 * dpn1 + h2 * dpn2, inv = 1.f / len;
+        dpn0 = (dpn0 - h0 * d) * inv; dpn1 = (dpn1 - h1 * d) * inv; dpn2 = (dpn2 - h2 * d) * inv;
+      } else {
+        dpn0 *= 1e12f; dpn1 *= 1e12f; dpn2 *= 1e12f;
+      }
+    }
     dpa = a.dL_dalpha[pix];
     if (ED >= 1) dpe0 = a.dL_dextra[pix];
   }

@@ -8,6 +8,7 @@ runs unmodified.  PyTorch supplies device memory, streams and autograd; every
 kernel is in libigs_raster.so (no fallback path exists).
 """
 import ctypes as C
+import threading
 from typing import NamedTuple
 
 import torch
@@ -31,8 +32,15 @@ class _DeviceScratch:
         self.ctrl = None
         self.accum = None
         self.pinned = torch.zeros(4, dtype=torch.int32).pin_memory()
+        self.pinned_ptr = self.pinned.data_ptr()
         self.capacity_hint = {}
+        self.sizes = {}
         self.zero_imgs = {}
+        # argument blocks are reused call after call (the library reads them before it returns)
+        self.fwd_args, self.bwd_args = N.IgsFwdArgs(), N.IgsBwdArgs()
+        self.fwd_args_ref, self.bwd_args_ref = C.byref(self.fwd_args), C.byref(self.bwd_args)
+        self.n_out = C.c_int64(0)
+        self.n_out_ref = C.byref(self.n_out)
 
     def buf(self, name, nbytes):
         t = getattr(self, name)
@@ -53,11 +61,32 @@ class _DeviceScratch:
 _scratch = {}
 
 
-def _get_scratch(device):
-    s = _scratch.get(device)
+def _get_scratch(device, stream=0):
+    """Scratch is private to a (device, stream, host thread): calls on different streams may run
+    concurrently on the GPU and must not share the sort / control / accumulator buffers."""
+    key = (device, stream, threading.get_ident())
+    s = _scratch.get(key)
     if s is None:
-        s = _scratch[device] = _DeviceScratch(device)
+        s = _scratch[key] = _DeviceScratch(device)
     return s
+
+
+class _NullCtx:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *exc):
+        return False
+
+
+_NULL_CTX = _NullCtx()
+
+
+def _on_device(dev):
+    """torch.cuda.device(dev) only when dev is not already the current device."""
+    if dev.index is None or dev.index == torch.cuda.current_device():
+        return _NULL_CTX
+    return torch.cuda.device(dev)
 
 
 def _ptr(t):
@@ -89,8 +118,10 @@ class GaussianRasterizationSettings(NamedTuple):
 
 def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier,
                     cov3Ds_precomp, norm3Ds_precomp, extra_attrs, ED, viewmatrix, projmatrix, tanfovx,
-                    tanfovy, image_height, image_width, sh, sh_degree, campos, prefiltered, debug):
-    """Equivalent of _C.rasterize_gaussians (DGR rasterize_points.cu:35-133)."""
+                    tanfovy, image_height, image_width, sh, sh_degree, campos, prefiltered, debug,
+                    normalize_norm=False):
+    """Equivalent of _C.rasterize_gaussians (DGR rasterize_points.cu:35-133).  normalize_norm: the
+    kernel also applies the F.normalize(norm, dim=0) of DGR diff_gauss/__init__.py:48."""
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     if not means3D.is_cuda:
@@ -99,53 +130,59 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
     dev = means3D.device
     P, H, W = means3D.size(0), int(image_height), int(image_width)
     M = sh.size(1) if sh.numel() != 0 else 0
-    f32 = dict(dtype=torch.float32, device=dev)
-    u8 = dict(dtype=torch.uint8, device=dev)
-    color = torch.empty((3, H, W), **f32)
-    depth = torch.empty((1, H, W), **f32)
-    norm = torch.empty((3, H, W), **f32)
-    alpha = torch.empty((1, H, W), **f32)
-    extra = torch.empty((ED, H, W), **f32) if ED > 0 else torch.empty((0,), **f32)
-    radii = torch.empty((P,), dtype=torch.int32, device=dev)
+    empty = torch.empty
+    color = empty((3, H, W), dtype=torch.float32, device=dev)
+    depth = empty((1, H, W), dtype=torch.float32, device=dev)
+    norm = empty((3, H, W), dtype=torch.float32, device=dev)
+    alpha = empty((1, H, W), dtype=torch.float32, device=dev)
+    extra = empty((ED, H, W) if ED > 0 else (0,), dtype=torch.float32, device=dev)
+    radii = empty((P,), dtype=torch.int32, device=dev)
 
-    sc = _get_scratch(dev)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    sc = _get_scratch(dev, stream)
     hint_key = (P, H, W)
+    sizes = sc.sizes.get(hint_key)
+    if sizes is None:
+        sizes = sc.sizes[hint_key] = (lib.igs_geom_bytes(P), lib.igs_img_bytes(W, H), lib.igs_ctrl_bytes(P, W, H))
+    geom_bytes, img_bytes, ctrl_bytes = sizes
     capacity = sc.capacity_hint.get(hint_key)
     if capacity is None:
         capacity = max(8 * P, 1 << 16)
-    geom = torch.empty(lib.igs_geom_bytes(P), **u8)
-    img = torch.empty(lib.igs_img_bytes(W, H), **u8)
-    binb = torch.empty(lib.igs_bin_bytes(capacity), **u8)
+    # forward state kept for backward: one allocation, [geom | img] (both sizes are multiples of 256)
+    state = empty((geom_bytes + img_bytes,), dtype=torch.uint8, device=dev)
+    geom, img = state[:geom_bytes], state[geom_bytes:]
+    binb = empty((lib.igs_bin_bytes(capacity),), dtype=torch.uint8, device=dev)
     sort = sc.buf("sort", lib.igs_sort_bytes(capacity))
-    ctrl = sc.buf("ctrl", lib.igs_ctrl_bytes(P, W, H))
+    ctrl = sc.buf("ctrl", ctrl_bytes)
 
-    keep = [_f32c(bg), _f32c(viewmatrix), _f32c(projmatrix), _f32c(campos), _f32c(means3D), _f32c(sh),
+    keep = (_f32c(bg), _f32c(viewmatrix), _f32c(projmatrix), _f32c(campos), _f32c(means3D), _f32c(sh),
             _f32c(colors_precomp), _f32c(opacities), _f32c(scales), _f32c(rotations),
-            _f32c(cov3Ds_precomp), _f32c(norm3Ds_precomp), _f32c(extra_attrs)]
-    a = N.IgsFwdArgs()
+            _f32c(cov3Ds_precomp), _f32c(norm3Ds_precomp), _f32c(extra_attrs))
+    a = sc.fwd_args
     a.P, a.D, a.M, a.ED, a.W, a.H = P, int(sh_degree), M, ED, W, H
     a.tan_fovx, a.tan_fovy, a.scale_modifier = tanfovx, tanfovy, scale_modifier
-    a.prefiltered, a.debug = int(bool(prefiltered)), int(bool(debug))
+    a.prefiltered, a.debug, a.normalize_norm = int(bool(prefiltered)), int(bool(debug)), int(bool(normalize_norm))
     (a.bg, a.viewmatrix, a.projmatrix, a.campos, a.means3D, a.shs, a.colors_precomp, a.opacities, a.scales,
      a.rotations, a.cov3Ds_precomp, a.norm3Ds_precomp, a.extra_attrs) = [_ptr(t) for t in keep]
     a.out_color, a.out_depth, a.out_norm, a.out_alpha = color.data_ptr(), depth.data_ptr(), norm.data_ptr(), alpha.data_ptr()
     a.out_extra = _ptr(extra)
     a.radii = radii.data_ptr() if P > 0 else None
-    a.geom, a.img, a.bin, a.sort, a.ctrl = geom.data_ptr(), img.data_ptr(), binb.data_ptr(), sort.data_ptr(), ctrl.data_ptr()
+    geom_ptr = state.data_ptr()
+    a.geom, a.img, a.bin, a.sort, a.ctrl = geom_ptr, geom_ptr + geom_bytes, binb.data_ptr(), sort.data_ptr(), ctrl.data_ptr()
     a.capacity = capacity
-    a.num_rendered_pinned = sc.pinned.data_ptr()
+    a.num_rendered_pinned = sc.pinned_ptr
 
-    stream = torch.cuda.current_stream(dev).cuda_stream
-    n = C.c_int64(0)
-    with torch.cuda.device(dev):
-        st = lib.igs_forward(C.byref(a), stream, C.byref(n))
+    n = sc.n_out
+    with _on_device(dev):
+        st = lib.igs_forward(sc.fwd_args_ref, stream, sc.n_out_ref)
         if st == N.IGS_ERR_CAPACITY:
             capacity = int(n.value * 1.1) + 4096
-            binb = torch.empty(lib.igs_bin_bytes(capacity), **u8)
+            binb = empty((lib.igs_bin_bytes(capacity),), dtype=torch.uint8, device=dev)
             sort = sc.buf("sort", lib.igs_sort_bytes(capacity))
             a.bin, a.sort, a.capacity = binb.data_ptr(), sort.data_ptr(), capacity
-            st = lib.igs_forward_bin_render(C.byref(a), stream)
-        N.check(st, "forward")
+            st = lib.igs_forward_bin_render(sc.fwd_args_ref, stream)
+        if st != N.IGS_OK:
+            N.check(st, "forward")
     num_rendered = int(n.value)
     # next call with this shape: 25 % head-room over what this one needed
     sc.capacity_hint[hint_key] = max(int(num_rendered * 1.25) + 4096, 1 << 14)
@@ -155,15 +192,17 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
 def _backward_native(bg, means3D, radii, colors_precomp, scales, rotations, extra_attrs, scale_modifier,
                      cov3Ds_precomp, norm3Ds_precomp, viewmatrix, projmatrix, tanfovx, tanfovy,
                      dL_dcolor, dL_ddepth, dL_dnorm, dL_dalpha, dL_dextra, sh, sh_degree, campos, geom,
-                     num_rendered, binb, img, alpha, debug):
-    """Equivalent of _C.rasterize_gaussians_backward (DGR rasterize_points.cu:135-239)."""
+                     num_rendered, binb, img, alpha, debug, norm_out=None):
+    """Equivalent of _C.rasterize_gaussians_backward (DGR rasterize_points.cu:135-239).  norm_out: the
+    unit normals a normalize_norm forward returned; dL_dnorm is then the gradient w.r.t. them."""
     lib = N.lib()
     dev = means3D.device
     P = means3D.size(0)
     H, W = alpha.size(1), alpha.size(2)
     ED = extra_attrs.size(1) if extra_attrs.numel() != 0 else 0
     M = sh.size(1) if sh.numel() != 0 else 0
-    sc = _get_scratch(dev)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    sc = _get_scratch(dev, stream)
     # one allocation for all per-Gaussian gradients, contiguous sub-blocks
     widths = [3, 3, 1, 3, 6, 3, 3 * M, 3, 4, ED]
     # (every block starts 16-byte aligned, as the C ABI requires)
@@ -187,9 +226,11 @@ def _backward_native(bg, means3D, radii, colors_precomp, scales, rotations, extr
             _f32c(norm3Ds_precomp), _f32c(extra_attrs), radii, geom, img, binb, _f32c(alpha),
             grad(dL_dcolor, 3), grad(dL_ddepth, 1), grad(dL_dnorm, 3), grad(dL_dalpha, 1),
             grad(dL_dextra, ED) if ED > 0 else None]
-    a = N.IgsBwdArgs()
+    a = sc.bwd_args
     a.P, a.D, a.M, a.ED, a.W, a.H = P, int(sh_degree), M, ED, W, H
     a.tan_fovx, a.tan_fovy, a.scale_modifier, a.debug = tanfovx, tanfovy, scale_modifier, int(bool(debug))
+    a.normalize_norm = int(norm_out is not None)
+    a.out_norm = _ptr(_f32c(norm_out)) if norm_out is not None else None
     a.num_rendered = num_rendered
     (a.bg, a.viewmatrix, a.projmatrix, a.campos, a.means3D, a.shs, a.colors_precomp, a.scales, a.rotations,
      a.cov3Ds_precomp, a.norm3Ds_precomp, a.extra_attrs, a.radii, a.geom, a.img, a.bin, a.out_alpha,
@@ -199,13 +240,17 @@ def _backward_native(bg, means3D, radii, colors_precomp, scales, rotations, extr
      a.dL_dscales, a.dL_drotations, a.dL_dextra_attrs) = [_ptr(t) for t in
                                                           (g_means2D, g_colors, g_opacity, g_means3D, g_cov3D,
                                                            g_norm3D, g_sh, g_scales, g_rot, g_extra)]
-    with torch.cuda.device(dev):
-        N.check(lib.igs_backward(C.byref(a), torch.cuda.current_stream(dev).cuda_stream), "backward")
+    with _on_device(dev):
+        st = lib.igs_backward(sc.bwd_args_ref, stream)
+        if st != N.IGS_OK:
+            N.check(st, "backward")
     return g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_norm3D, g_sh, g_scales, g_rot, g_extra
 
 
 class _RasterizeGaussians(torch.autograd.Function):
     # DGR diff_gauss/__init__.py:52-178
+    FUSE_NORMALIZE = False  # the reference Function returns the un-normalised normal image
+
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                 norm3Ds_precomp, extra_attrs, raster_settings):
@@ -217,7 +262,7 @@ class _RasterizeGaussians(torch.autograd.Function):
             raster_settings.viewmatrix, raster_settings.projmatrix, raster_settings.tanfovx,
             raster_settings.tanfovy, raster_settings.image_height, raster_settings.image_width, sh,
             raster_settings.sh_degree, raster_settings.campos, raster_settings.prefiltered,
-            raster_settings.debug)
+            raster_settings.debug, ctx._forward_cls.FUSE_NORMALIZE)
         if raster_settings.debug:
             cpu_args = cpu_deep_copy_tuple(args)  # copy them before they can be corrupted
             try:
@@ -233,8 +278,10 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.num_rendered = num_rendered
         ctx.set_materialize_grads(False)
         ctx.mark_non_differentiable(radii)
-        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, norm3Ds_precomp,
-                              radii, extra_attrs, sh, geomBuffer, binningBuffer, imgBuffer, alpha)
+        ctx.fused_norm = ctx._forward_cls.FUSE_NORMALIZE
+        saved = (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, norm3Ds_precomp,
+                 radii, extra_attrs, sh, geomBuffer, binningBuffer, imgBuffer, alpha)
+        ctx.save_for_backward(*(saved + ((norm,) if ctx.fused_norm else ())))
         return color, depth, norm, alpha, radii, extra
 
     @staticmethod
@@ -242,13 +289,14 @@ class _RasterizeGaussians(torch.autograd.Function):
         num_rendered = ctx.num_rendered
         raster_settings = ctx.raster_settings
         (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, norm3Ds_precomp, radii, extra_attrs, sh,
-         geomBuffer, binningBuffer, imgBuffer, alpha) = ctx.saved_tensors
+         geomBuffer, binningBuffer, imgBuffer, alpha) = ctx.saved_tensors[:13]
+        norm_out = ctx.saved_tensors[13] if ctx.fused_norm else None
         args = (raster_settings.bg, means3D, radii, colors_precomp, scales, rotations, extra_attrs,
                 raster_settings.scale_modifier, cov3Ds_precomp, norm3Ds_precomp, raster_settings.viewmatrix,
                 raster_settings.projmatrix, raster_settings.tanfovx, raster_settings.tanfovy, grad_out_color,
                 grad_out_depth, grad_out_norm, grad_out_alpha, grad_out_extra, sh, raster_settings.sh_degree,
                 raster_settings.campos, geomBuffer, num_rendered, binningBuffer, imgBuffer, alpha,
-                raster_settings.debug)
+                raster_settings.debug, norm_out)
         if raster_settings.debug:
             cpu_args = cpu_deep_copy_tuple(args)
             try:
@@ -268,14 +316,19 @@ class _RasterizeGaussians(torch.autograd.Function):
         return tuple(g if (g is not None and need) else None for g, need in zip(grads, ctx.needs_input_grad))
 
 
+class _RasterizeGaussiansUnitNormal(_RasterizeGaussians):
+    """Same Function with the reference's trailing `norm = F.normalize(norm, p=2, dim=0)`
+    (DGR diff_gauss/__init__.py:48) done inside the render kernels, forward and backward: three
+    element-wise kernels, six backward kernels and four autograd nodes less per call."""
+    FUSE_NORMALIZE = True
+
+
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                         norm3Ds_precomp, extra_attrs, raster_settings):
-    # DGR diff_gauss/__init__.py:21-50
-    color, depth, norm, alpha, radii, extra = _RasterizeGaussians.apply(
+    # DGR diff_gauss/__init__.py:21-50; the F.normalize of :48 is fused into the kernels
+    return _RasterizeGaussiansUnitNormal.apply(
         means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, norm3Ds_precomp,
         extra_attrs, raster_settings)
-    norm = torch.nn.functional.normalize(norm, p=2, dim=0)
-    return color, depth, norm, alpha, radii, extra
 
 
 class GaussianRasterizer(nn.Module):

@@ -259,6 +259,7 @@ def main():
     import torch.distributed as dist
     import util as U
     from instag_b200 import synthetic as S
+    from instag_b200 import sharding as SHD
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -294,7 +295,7 @@ def main():
             return arm.step_fwd_only()
         res = arm.step_raw()
         if eff_world > 1:
-            dist.all_reduce(res[0]._base if res[0]._base is not None else res[0])  # packed per-Gaussian grads
+            SHD.allreduce_view_gradients(res)  # ONE all-reduce: the ten gradients share one allocation
         return res
 
     def step_e2e():
@@ -435,7 +436,9 @@ def synth_fps(torch, dist, world, rank, flush, device, frames=60):
     import util as U
     from instag_b200 import synthetic as S
     from instag_b200 import rasterizer as R
-    cams = S.camera_sequence(frames * world, 512, 512, seed=3)[rank::world]
+    from instag_b200 import sharding as SHD
+    all_cams = S.camera_sequence(frames * world, 512, 512, seed=3)
+    cams = [all_cams[i] for i in SHD.shard_indices(frames * world, rank, world)]
     clouds = [S.make_cloud(100_000, sh_degree=1, M=4, seed=0), S.make_cloud(30_000, sh_degree=1, M=4, seed=1)]
     tcl = [U.to_torch(c, device) for c in clouds]
     scenes = []

@@ -68,6 +68,18 @@ struct EventCache { // one reusable event per host thread
 };
 static thread_local EventCache g_event;
 
+// device-side address of a pinned host slot (cached per host thread; NULL if it is not mapped)
+static int32_t* device_view_of_pinned(int32_t* host) {
+  static thread_local int32_t* last_host = nullptr;
+  static thread_local int32_t* last_dev = nullptr;
+  if (host == last_host) return last_dev;
+  void* d = nullptr;
+  if (cudaHostGetDevicePointer(&d, host, 0) != cudaSuccess) { cudaGetLastError(); d = nullptr; }
+  last_host = host;
+  last_dev = (int32_t*)d;
+  return last_dev;
+}
+
 static int validate_fwd(const IgsFwdArgs* a) {
   if (!a) { set_error("null args"); return IGS_ERR_INVALID; }
   if (a->P < 0 || a->W <= 0 || a->H <= 0) { set_error("bad sizes P=%d W=%d H=%d", a->P, a->W, a->H); return IGS_ERR_INVALID; }
@@ -117,6 +129,7 @@ static PreArgs make_pre(const IgsFwdArgs* a) {
   p.clamped = (uint8_t*)(g + gl.clamped);
   p.scan_state = (unsigned long long*)(c + cl.scan_state);
   p.header = (CtrlHeader*)(c + cl.header);
+  p.num_rendered_host = device_view_of_pinned(a->num_rendered_pinned);
   p.tile_count = (uint32_t*)(c + cl.tile_count);
   p.tile_cursor = (uint32_t*)(c + cl.tile_cursor);
   p.ranges = (uint2*)((char*)a->img + ImgLayout(a->W, a->H).ranges);
@@ -230,8 +243,9 @@ int igs_forward(const IgsFwdArgs* a, igs_stream_t stream, int64_t* num_rendered)
   launch_preprocess(pa, s);
   prof_mark(1, s);
   if (int r = stage_check(debug, s, "preprocess")) return r;
-  if (int r = check_cuda(cudaMemcpyAsync(a->num_rendered_pinned, &pa.header->num_rendered, sizeof(int32_t),
-                                         cudaMemcpyDeviceToHost, s), "copy num_rendered")) return r;
+  if (!pa.num_rendered_host) // slot not device-mapped: fall back to a copy-engine transfer
+    if (int r = check_cuda(cudaMemcpyAsync(a->num_rendered_pinned, &pa.header->num_rendered, sizeof(int32_t),
+                                           cudaMemcpyDeviceToHost, s), "copy num_rendered")) return r;
   cudaEvent_t ev = g_event.get();
   if (int r = check_cuda(cudaEventRecord(ev, s), "event record")) return r;
   // speculative second half: sized by capacity, bounded on the device by num_rendered

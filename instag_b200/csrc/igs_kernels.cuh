@@ -18,6 +18,7 @@ struct PreArgs {
   uint8_t* clamped;
   unsigned long long* scan_state;
   CtrlHeader* header;
+  int32_t* num_rendered_host; // device view of the caller's pinned slot (NULL: the host copies it)
   uint32_t* tile_count;   // [T*CNT_STRIDE] instances per tile (atomics), zeroed by the caller
   uint32_t* tile_cursor;  // [T*CNT_STRIDE] next free slot of each tile segment (written by the last CTA)
   uint2* ranges;          // [T] [start, end) of each tile in the sorted list, (0,0) if empty

@@ -237,6 +237,9 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
       s_excl = excl;
       if (bid == (int)gridDim.x - 1) {
         a.header->num_rendered = excl + total;
+        // straight into the caller's pinned host slot: a 4-byte copy-engine transfer between two
+        // kernels costs ~12 us of stream time on B200, a posted store costs nothing
+        if (a.num_rendered_host) *(volatile int32_t*)a.num_rendered_host = (int32_t)(excl + total);
         a.header->overflow = (int64_t)(excl + total) > a.capacity ? 1u : 0u;
       }
     }

@@ -127,7 +127,8 @@ static PreArgs make_pre(const IgsFwdArgs* a) {
   p.tiles_touched = (uint32_t*)(g + gl.tiles_touched);
   p.point_offsets = (uint32_t*)(g + gl.point_offsets);
   p.clamped = (uint8_t*)(g + gl.clamped);
-  p.scan_state = (unsigned long long*)(c + cl.scan_state);
+  p.block_total = (uint32_t*)(c + cl.scan_state);
+  p.block_prefix = p.block_total + (a->P + PRE_THREADS - 1) / PRE_THREADS;
   p.header = (CtrlHeader*)(c + cl.header);
   p.num_rendered_host = device_view_of_pinned(a->num_rendered_pinned);
   p.tile_count = (uint32_t*)(c + cl.tile_count);
@@ -153,6 +154,8 @@ static BinArgs make_bin(const IgsFwdArgs* a) {
   ba.radii = a->radii;
   ba.splat = (const float4*)(g + gl.splat);
   ba.tiles_touched = (const uint32_t*)(g + gl.tiles_touched);
+  ba.point_offsets = (uint32_t*)(g + gl.point_offsets);
+  ba.block_prefix = (const uint32_t*)(c + cl.scan_state) + (a->P + PRE_THREADS - 1) / PRE_THREADS;
   ba.header = (CtrlHeader*)(c + cl.header);
   ba.tile_cursor = (uint32_t*)(c + cl.tile_cursor);
   ba.ranges = (const uint2*)(im + il.ranges);
@@ -162,11 +165,12 @@ static BinArgs make_bin(const IgsFwdArgs* a) {
   return ba;
 }
 
-static int run_bin_render(const IgsFwdArgs* a, cudaStream_t s) {
+static int run_bin_render(const IgsFwdArgs* a, cudaStream_t s, bool rerun = false) {
   const ImgLayout il(a->W, a->H);
   char* im = (char*)a->img;
   const bool debug = a->debug != 0;
-  const BinArgs ba = make_bin(a);
+  BinArgs ba = make_bin(a);
+  if (rerun) ba.block_prefix = nullptr; // point_offsets were made global by the first pass
   launch_binning(ba, s);
   if (int r = stage_check(debug, s, "binning (duplicate/tile sort)")) return r;
 
@@ -269,7 +273,7 @@ int igs_forward_bin_render(const IgsFwdArgs* a, igs_stream_t stream) {
   if (int r = check_cuda(cudaMemsetAsync(&ba.header->overflow, 0, sizeof(uint32_t), s), "clear overflow")) return r;
   if (int r = check_cuda(cudaMemsetAsync(&ba.header->render_ticket, 0, sizeof(uint32_t), s), "clear ticket")) return r;
   launch_reset_cursors(ba, s);
-  return run_bin_render(a, s);
+  return run_bin_render(a, s, true);
 }
 
 int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {

@@ -81,7 +81,11 @@ __global__ void __launch_bounds__(DUP_THREADS) duplicate_kernel(BinArgs a) {
   if (HIST_SMEM)
     for (int t = tid; t < a.num_tiles; t += DUP_THREADS) s_slot[t] = 0u;
   uint32_t n = 0, xy = 0, w = 1, depth = 0;
-  if (g < a.P) n = __ldg(a.tiles_touched + g);
+  if (g < a.P) {
+    n = __ldg(a.tiles_touched + g);
+    // reference point_offsets (InclusiveSum, rasterizer_impl.cu:280): CTA-local scan + CTA prefix
+    if (a.block_prefix) a.point_offsets[g] += __ldcg(a.block_prefix + blockIdx.x);
+  }
   if (n) {
     const float4 r1 = __ldg(a.splat + (size_t)g * SPLAT_F4 + 1); // x, y, depth, extra0
     int x0, y0, x1, y1;

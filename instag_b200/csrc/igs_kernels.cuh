@@ -16,7 +16,8 @@ struct PreArgs {
   uint32_t* tiles_touched;
   uint32_t* point_offsets;
   uint8_t* clamped;
-  unsigned long long* scan_state;
+  uint32_t* block_total;   // [ceil(P/PRE_THREADS)] sum of tiles_touched per preprocess CTA
+  uint32_t* block_prefix;  // [same] exclusive scan of block_total (written by the last CTA)
   CtrlHeader* header;
   int32_t* num_rendered_host; // device view of the caller's pinned slot (NULL: the host copies it)
   uint32_t* tile_count;   // [T*CNT_STRIDE] instances per tile (atomics), zeroed by the caller
@@ -31,6 +32,8 @@ struct BinArgs {
   const int32_t* radii;
   const float4* splat;
   const uint32_t* tiles_touched;
+  uint32_t* point_offsets;       // CTA-local inclusive scan from preprocess; made global here
+  const uint32_t* block_prefix;  // NULL on a re-run after IGS_ERR_CAPACITY (offsets already global)
   CtrlHeader* header;
   uint32_t* tile_cursor;      // [T*CNT_STRIDE]
   const uint2* ranges;        // [T]

@@ -60,58 +60,25 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float* __restrict__ s
   return make_float3(res[0], res[1], res[2]);
 }
 
-// ---- single-pass inclusive scan state (decoupled look-back) ----------------
-// 64-bit word per CTA: high 32 bits = flag (0 empty, 1 aggregate, 2 inclusive
-// prefix), low 32 bits = value.  One 64-bit store/load keeps them consistent.
 constexpr int ORDER_BUCKETS = 2 * PRE_THREADS;
-constexpr unsigned long long FLAG_AGG = 1ull << 32, FLAG_PREFIX = 2ull << 32;
 
-__device__ __forceinline__ unsigned long long ld_state(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
+#ifdef IGS_PRE_TRACE
+__device__ unsigned long long g_pre_trace[8 * 4096];
+__device__ __forceinline__ unsigned long long pre_timer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
 }
-__device__ __forceinline__ void st_state(unsigned long long* p, unsigned long long v) {
-  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-
-// Exclusive prefix of this CTA's total over all previous CTAs; executed by
-// warp 0.  Windows of 32 predecessors are inspected at once.
-__device__ __forceinline__ uint32_t lookback_exclusive(unsigned long long* state, int bid, uint32_t total) {
-  const int lane = threadIdx.x & 31;
-  if (bid == 0) {
-    if (lane == 0) st_state(state, FLAG_PREFIX | total);
-    return 0;
-  }
-  if (lane == 0) st_state(state + bid, FLAG_AGG | total);
-  uint32_t excl = 0;
-  int base = bid - 1;
-  while (true) {
-    const int j = base - lane;
-    unsigned long long v = j >= 0 ? ld_state(state + j) : FLAG_PREFIX; // virtual prefix 0 before CTA 0
-    const uint32_t flag = (uint32_t)(v >> 32);
-    const unsigned ready = __ballot_sync(0xffffffffu, flag != 0);
-    const unsigned pref = __ballot_sync(0xffffffffu, flag == 2);
-    // lanes 0..first-1 must all be ready, where first = nearest lane holding a prefix
-    const int first = pref ? __ffs(pref) - 1 : 32;
-    const unsigned need = first >= 31 ? 0xffffffffu : ((2u << first) - 1);
-    if ((ready & need) != need) continue; // somebody in the window has not published yet
-    uint32_t val = (lane <= first) ? (uint32_t)v : 0u;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
-    excl += val;
-    if (pref) break;
-    base -= 32;
-  }
-  if (lane == 0) st_state(state + bid, FLAG_PREFIX | (unsigned long long)(uint32_t)(excl + total));
-  return excl;
-}
+#define PRE_MARK(k) do { if (threadIdx.x == 0) g_pre_trace[8 * blockIdx.x + (k)] = pre_timer(); } while (0)
+#else
+#define PRE_MARK(k) do { } while (0)
+#endif
 
 template <bool USE_SH, bool HIST_SMEM>
 __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   __shared__ uint32_t s_warp_sum[PRE_THREADS / 32];
-  __shared__ uint32_t s_excl, s_bid, s_last;
+  __shared__ uint32_t s_last;
   // CTA-local histogram of the instances per tile (HIST_SMEM: the launch gave us 4*T bytes):
   // one global RED per (CTA, non-empty tile) instead of one per instance
   extern __shared__ uint32_t s_hist[];
@@ -121,17 +88,25 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
     for (int t = tid; t < T; t += PRE_THREADS) s_hist[t] = 0u;
   if (tid < 16) { s_view[tid] = __ldg(a.viewmatrix + tid); s_proj[tid] = __ldg(a.projmatrix + tid); }
   if (tid < 3) s_cam[tid] = __ldg(a.campos + tid);
-  // the chunk a CTA works on is handed out in START order, so the CTA a look-back waits
-  // for is always already running (no assumption about the hardware's CTA dispatch order)
-  if (tid == 0) s_bid = atomicAdd(&a.header->ticket, 1u);
+  PRE_MARK(0);
   __syncthreads();
-  const int bid = (int)s_bid;
+  PRE_MARK(1);
+  const int bid = (int)blockIdx.x;
 
   const int idx = bid * PRE_THREADS + tid;
   uint32_t tiles = 0;
   int radius = 0;
   if (idx < a.P) {
+    // every input of this Gaussian is requested up front (one DRAM round trip instead of three
+    // dependent ones); the few that turn out to be culled cost 44 B of bandwidth
     const float px = __ldg(a.means3D + 3 * idx), py = __ldg(a.means3D + 3 * idx + 1), pz = __ldg(a.means3D + 3 * idx + 2);
+    const float3 sc = make_float3(__ldg(a.scales + 3 * idx), __ldg(a.scales + 3 * idx + 1), __ldg(a.scales + 3 * idx + 2));
+    const float4 q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
+    const float op = __ldg(a.opacities + idx);
+    const float e0 = a.extra_attrs ? __ldg(a.extra_attrs + (size_t)idx * a.ED) : 0.f;
+    float3 rgb = make_float3(0.f, 0.f, 0.f);
+    if (!USE_SH) rgb = make_float3(__ldg(a.colors_precomp + 3 * idx), __ldg(a.colors_precomp + 3 * idx + 1),
+                                   __ldg(a.colors_precomp + 3 * idx + 2));
     const float vz = xform_row(s_view, 2, px, py, pz);
     if (vz <= NEAR_Z) { // reference auxiliary.h:155 (NaN passes, as there)
       if (a.prefiltered) { printf("Point is filtered although prefiltered is set. This shouldn't happen!"); __trap(); }
@@ -141,8 +116,6 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
       const float p_w = __fdiv_rn(1.0f, __fadd_rn(hw, 0.0000001f));
       const float ndc_x = __fmul_rn(hx, p_w), ndc_y = __fmul_rn(hy, p_w);
 
-      const float3 sc = make_float3(__ldg(a.scales + 3 * idx), __ldg(a.scales + 3 * idx + 1), __ldg(a.scales + 3 * idx + 2));
-      const float4 q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
       const Rot R = quat_to_rot(q);
       float c3[6];
       if (a.cov3Ds_precomp) {
@@ -186,7 +159,6 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
             const float rx = __fsub_rn(px, s_cam[0]), ry = __fsub_rn(py, s_cam[1]), rz = __fsub_rn(pz, s_cam[2]);
             if (dot3c(rx, nx, ry, ny, rz, nz) > 0.f) { nx = -nx; ny = -ny; nz = -nz; }
           }
-          float3 rgb;
           if (USE_SH) {
             float dx = __fsub_rn(px, s_cam[0]), dy = __fsub_rn(py, s_cam[1]), dz = __fsub_rn(pz, s_cam[2]);
             const float len = __fsqrt_rn(dot3c(dx, dx, dy, dy, dz, dz));
@@ -194,17 +166,11 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
             uint32_t mask = 0;
             rgb = sh_to_rgb(a.D, a.shs + (size_t)idx * a.M * 3, dx, dy, dz, mask);
             a.clamped[idx] = (uint8_t)mask;
-          } else {
-            rgb = make_float3(__ldg(a.colors_precomp + 3 * idx), __ldg(a.colors_precomp + 3 * idx + 1),
-                              __ldg(a.colors_precomp + 3 * idx + 2));
           }
-          const float e0 = a.extra_attrs ? __ldg(a.extra_attrs + (size_t)idx * a.ED) : 0.f;
           float4* rec = a.splat + (size_t)idx * SPLAT_F4;
-          rec[0] = make_float4(__fmul_rn(cov.z, det_inv), __fmul_rn(-cov.y, det_inv), __fmul_rn(cov.x, det_inv),
-                               __ldg(a.opacities + idx));
+          rec[0] = make_float4(__fmul_rn(cov.z, det_inv), __fmul_rn(-cov.y, det_inv), __fmul_rn(cov.x, det_inv), op);
           rec[1] = make_float4(sx, sy, vz, e0);
           rec[2] = make_float4(rgb.x, rgb.y, rgb.z, nx);
-          const float op = __ldg(a.opacities + idx);
           rec[3] = make_float4(ny, nz, 2.f * logf(255.f * op), 0.f); // culling bound, see splat_may_touch
         }
       }
@@ -213,6 +179,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
     a.tiles_touched[idx] = tiles;
   }
 
+  PRE_MARK(2);
   // block inclusive scan of `tiles`
   uint32_t incl = tiles;
 #pragma unroll
@@ -232,20 +199,13 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
     }
     const uint32_t total = __shfl_sync(0xffffffffu, wi, PRE_THREADS / 32 - 1);
     if (lane < PRE_THREADS / 32) s_warp_sum[lane] = wi - w; // exclusive warp offsets
-    const uint32_t excl = lookback_exclusive(a.scan_state, bid, total);
-    if (lane == 0) {
-      s_excl = excl;
-      if (bid == (int)gridDim.x - 1) {
-        a.header->num_rendered = excl + total;
-        // straight into the caller's pinned host slot: a 4-byte copy-engine transfer between two
-        // kernels costs ~12 us of stream time on B200, a posted store costs nothing
-        if (a.num_rendered_host) *(volatile int32_t*)a.num_rendered_host = (int32_t)(excl + total);
-        a.header->overflow = (int64_t)(excl + total) > a.capacity ? 1u : 0u;
-      }
-    }
+    // no look-back chain: the CTA publishes its total, the last CTA scans the totals, and the
+    // duplicate kernel adds the CTA's prefix to these CTA-local offsets
+    if (lane == 0) a.block_total[bid] = total;
   }
   __syncthreads();
-  if (idx < a.P) a.point_offsets[idx] = s_excl + s_warp_sum[warp] + incl;
+  PRE_MARK(3);
+  if (idx < a.P) a.point_offsets[idx] = s_warp_sum[warp] + incl;
   if (HIST_SMEM) { // (the barrier above ordered every thread's shared-memory atomics)
     for (int t = tid; t < T; t += PRE_THREADS) {
       const uint32_t c = s_hist[t];
@@ -258,46 +218,86 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
   // range of a tile is [exclusive prefix of the counts, +count), (0,0) for an empty tile)
   __threadfence();
   __syncthreads();
+  PRE_MARK(4);
   if (tid == 0) s_last = atomicAdd(&a.header->done, 1u) == gridDim.x - 1 ? 1u : 0u;
   __syncthreads();
+  PRE_MARK(5);
   if (!s_last) return;
   __threadfence();
+  // (1) tile counts: one L2 round trip into shared memory (all requests in flight together);
+  //     later phases read them from there.  Beyond HIST_SMEM_MAX_TILES they stay in L2.
+  if (HIST_SMEM) {
+    for (int t = tid; t < T; t += PRE_THREADS) s_hist[t] = __ldcg(a.tile_count + (size_t)t * CNT_STRIDE);
+  }
+#define TILE_CNT(t) (HIST_SMEM ? s_hist[t] : __ldcg(a.tile_count + (size_t)(t) * CNT_STRIDE))
+  // (2) CTA totals of tiles_touched -> exclusive prefixes (added to point_offsets by the
+  //     duplicate kernel), num_rendered, overflow flag
+  const int nb = (int)gridDim.x;
+  const int bper = (nb + PRE_THREADS - 1) / PRE_THREADS;
+  const int b0 = min(nb, tid * bper), b1 = min(nb, b0 + bper);
+  uint32_t bsum = 0;
+  for (int b = b0; b < b1; b++) bsum += __ldcg(a.block_total + b);
+  uint32_t binc = bsum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t n = __shfl_up_sync(0xffffffffu, binc, o);
+    if (lane >= o) binc += n;
+  }
+  __syncthreads(); // s_warp_sum is reused; s_hist is complete
+  if (lane == 31) s_warp_sum[warp] = binc;
+  __syncthreads();
+  {
+    uint32_t run = binc - bsum, all = 0;
+    for (int w = 0; w < PRE_THREADS / 32; w++) {
+      if (w < warp) run += s_warp_sum[w];
+      all += s_warp_sum[w];
+    }
+    for (int b = b0; b < b1; b++) {
+      a.block_prefix[b] = run;
+      run += __ldcg(a.block_total + b);
+    }
+    if (tid == 0) {
+      a.header->num_rendered = all;
+      a.header->overflow = (int64_t)all > a.capacity ? 1u : 0u;
+      // straight into the caller's pinned host slot: a 4-byte copy-engine transfer between two
+      // kernels costs ~12 us of stream time on B200, a posted store costs nothing
+      if (a.num_rendered_host) *(volatile int32_t*)a.num_rendered_host = (int32_t)all;
+    }
+  }
+  // (3) tile counts -> ranges and cursors
   const int per = (T + PRE_THREADS - 1) / PRE_THREADS;
-  const int t0 = tid * per, t1 = min(T, t0 + per);
-  uint32_t sum = 0;
-  for (int t = t0; t < t1; t++) sum += __ldcg(a.tile_count + (size_t)t * CNT_STRIDE);
+  const int t0 = min(T, tid * per), t1 = min(T, t0 + per);
+  uint32_t sum = 0, cmax = 0;
+  for (int t = t0; t < t1; t++) { const uint32_t c = TILE_CNT(t); sum += c; cmax = max(cmax, c); }
   uint32_t inc = sum;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
     if (lane >= o) inc += n;
   }
-  __syncthreads(); // s_warp_sum is reused
-  if (lane == 31) s_warp_sum[warp] = inc;
-  __syncthreads();
-  uint32_t run = inc - sum;
-  for (int w = 0; w < warp; w++) run += s_warp_sum[w];
-  uint32_t cmax = 0;
-  for (int t = t0; t < t1; t++) {
-    const uint32_t c = __ldcg(a.tile_count + (size_t)t * CNT_STRIDE);
-    a.tile_cursor[(size_t)t * CNT_STRIDE] = run;
-    a.ranges[t] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
-    run += c;
-    cmax = max(cmax, c);
-  }
-  // ---- launch order of the render kernels: tiles with the longest lists first (their warps
-  // are the critical path), by one counting pass over ORDER_BUCKETS count classes ----
   __shared__ uint32_t s_bucket[ORDER_BUCKETS];
   __shared__ uint32_t s_max[PRE_THREADS / 32];
   cmax = __reduce_max_sync(0xffffffffu, cmax);
+  __syncthreads(); // s_warp_sum is reused
+  if (lane == 31) s_warp_sum[warp] = inc;
   if (lane == 0) s_max[warp] = cmax;
   for (int b = tid; b < ORDER_BUCKETS; b += PRE_THREADS) s_bucket[b] = 0u;
   __syncthreads();
+  uint32_t run = inc - sum;
+  for (int w = 0; w < warp; w++) run += s_warp_sum[w];
 #pragma unroll
   for (int w = 0; w < PRE_THREADS / 32; w++) cmax = max(cmax, s_max[w]);
+  // ---- launch order of the render kernels: tiles with the longest lists first (their warps
+  // are the critical path), by one counting pass over ORDER_BUCKETS count classes ----
   const float qs = (float)(ORDER_BUCKETS - 1) / (float)max(cmax, 1u);
 #define ORDER_BUCKET(c) ((ORDER_BUCKETS - 1) - min(ORDER_BUCKETS - 1, (int)((float)(c) * qs)))
-  for (int t = t0; t < t1; t++) atomicAdd(&s_bucket[ORDER_BUCKET(__ldcg(a.tile_count + (size_t)t * CNT_STRIDE))], 1u);
+  for (int t = t0; t < t1; t++) {
+    const uint32_t c = TILE_CNT(t);
+    a.tile_cursor[(size_t)t * CNT_STRIDE] = run;
+    a.ranges[t] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
+    run += c;
+    atomicAdd(&s_bucket[ORDER_BUCKET(c)], 1u);
+  }
   __syncthreads();
   { // exclusive scan of the bucket sizes (ORDER_BUCKETS == 2 * PRE_THREADS: two per thread)
     const uint32_t c0 = s_bucket[2 * tid], c1 = s_bucket[2 * tid + 1];
@@ -316,9 +316,11 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreArgs a) {
   }
   __syncthreads();
   for (int t = t0; t < t1; t++) {
-    const uint32_t slot = atomicAdd(&s_bucket[ORDER_BUCKET(__ldcg(a.tile_count + (size_t)t * CNT_STRIDE))], 1u);
+    const uint32_t slot = atomicAdd(&s_bucket[ORDER_BUCKET(TILE_CNT(t))], 1u);
     a.tile_order[slot] = (uint32_t)t;
   }
+#undef TILE_CNT
+  PRE_MARK(6);
 #undef ORDER_BUCKET
 }
 
@@ -347,6 +349,12 @@ void launch_preprocess(const PreArgs& a, cudaStream_t s) {
   }
   count_launch();
 }
+
+#ifdef IGS_PRE_TRACE
+extern "C" int igs_pre_trace_read(unsigned long long* host, int n) {
+  return (int)cudaMemcpyFromSymbol(host, g_pre_trace, sizeof(unsigned long long) * n);
+}
+#endif
 
 void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s) {
   if (P <= 0) return;

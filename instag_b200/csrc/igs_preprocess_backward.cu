@@ -55,18 +55,52 @@ __device__ __forceinline__ float3 sh_backward(int deg, int M, const float* __res
     }
   }
   const float gc[3] = {g.x, g.y, g.z};
+  if ((M & 3) == 0) {
+    // the row dL_dsh[idx] is 16-byte aligned: element e = 3k+c is w[k]*g[c] (0 beyond the active
+    // degree), written as 3M/4 float4 stores instead of 3M scalar ones at a 12*M-byte lane stride
+    float4* o = reinterpret_cast<float4*>(dsh);
+    const int nv = 3 * M / 4;
 #pragma unroll
-  for (int k = 0; k < 16; k++)
-    if (k < M) {
-      const float wk = k < n ? w[k] : 0.f;
-      dsh[3 * k] = wk * gc[0]; dsh[3 * k + 1] = wk * gc[1]; dsh[3 * k + 2] = wk * gc[2];
-    }
-  for (int k = 16; k < M; k++) { dsh[3 * k] = 0.f; dsh[3 * k + 1] = 0.f; dsh[3 * k + 2] = 0.f; }
+    for (int i = 0; i < 12; i++)
+      if (i < nv) {
+        float e[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          const int k = (4 * i + j) / 3, c = (4 * i + j) % 3;
+          e[j] = k < n ? w[k] * gc[c] : 0.f;
+        }
+        o[i] = make_float4(e[0], e[1], e[2], e[3]);
+      }
+    for (int i = 12; i < nv; i++) o[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  } else {
+#pragma unroll
+    for (int k = 0; k < 16; k++)
+      if (k < M) {
+        const float wk = k < n ? w[k] : 0.f;
+        dsh[3 * k] = wk * gc[0]; dsh[3 * k + 1] = wk * gc[1]; dsh[3 * k + 2] = wk * gc[2];
+      }
+    for (int k = 16; k < M; k++) { dsh[3 * k] = 0.f; dsh[3 * k + 1] = 0.f; dsh[3 * k + 2] = 0.f; }
+  }
   float3 dd = make_float3(0.f, 0.f, 0.f);
   if (deg > 0) {
+    float v[48];
+    const int need = 3 * n;
+    if ((M & 3) == 0) {
+      const float4* p = reinterpret_cast<const float4*>(sh);
+#pragma unroll
+      for (int i = 0; i < 12; i++)
+        if (4 * i < need) {
+          const float4 t = __ldg(p + i);
+          v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+        }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 48; j++)
+        if (j < need) v[j] = __ldg(sh + j);
+    }
 #pragma unroll
     for (int c = 0; c < 3; c++) {
-#define SHK(k) __ldg(sh + 3 * (k) + c)
+#define SHK(k) v[3 * (k) + c]
       float gx = -bSH_C1 * SHK(3), gy = -bSH_C1 * SHK(1), gz = bSH_C1 * SHK(2);
       if (deg > 1) {
         gx += bSH_C2[0] * y * SHK(4) + bSH_C2[2] * 2.f * -x * SHK(6) + bSH_C2[3] * z * SHK(7) + bSH_C2[4] * 2.f * x * SHK(8);

@@ -1,15 +1,24 @@
 // Backward of the compositing stage (reference renderCUDA, backward.cu:473-712).
 //
-// One CTA per tile, one thread per pixel, back-to-front traversal, T recovered
-// by division exactly as the reference does (backward.cu:612).  Where the
-// reference issues 13+ED global float atomics per accepted pixel-Gaussian pair,
-// this kernel first reduces the 14 partial gradients over the 32 pixels of a
-// warp with a TRANSPOSING butterfly (16 shuffles for 16 values instead of
-// 16*5), after which lane 2k holds the warp total of value k and the warp
-// issues one coalesced 14-lane red.global.add into the Gaussian's 64-byte
-// accumulator row.  Gaussians no lane of the warp touches are skipped with one
-// ballot; the tail of the list behind every pixel's last contributor is skipped
-// without being loaded.
+// One warp per 8x4 pixel block, one lane per pixel, back-to-front traversal, T
+// recovered by division exactly as the reference does (backward.cu:612).  Where
+// the reference issues 13+ED global float atomics per accepted pixel-Gaussian
+// pair, the sum over the warp's 32 pixels is done here as a small matrix product.
+// Per blended (pixel, splat) pair a lane produces just TWO scalars, the blend
+// weight w = alpha*T and g = G*dL/dalpha; every per-Gaussian gradient is linear in them:
+//     dL/dattr_k(s)  = sum_p w[s][p] * dL_dpixel_k[p]                (8 channels)
+//     moments(s)     = sum_p g[s][p] * {1, lx, lx^2, lx*ly, ly^2, ly}[p]   (lx, ly = pixel
+//                      offset inside the block; shifted to the splat centre afterwards)
+// i.e. [16 splats x 32 pixels] x [32 pixels x 8], with the right-hand matrix constant for
+// the whole unit.  w and g are parked in shared memory; every 16 parked splats the warp
+// runs the two products on the tensor cores (mma.sync m16n8k8 TF32, split into hi/lo
+// terms so that the result keeps fp32 accuracy: 3 terms against dL_dpixel, 2 against the
+// small-integer moment basis, which TF32 holds exactly) and adds the fragment to the
+// Gaussians' 64-byte accumulator rows with 8-byte vector REDs: 14 atomics per
+// (warp, splat) as before, but ~9 instructions per splat instead of the ~80 of a
+// shuffle butterfly over 16 partial products.  Gaussians no lane of the warp touches
+// are skipped with one ballot; the tail of the list behind every pixel's last
+// contributor is skipped without being loaded.
 //
 // Each warp first culls the staged splats against its own 8x4 pixel rectangle
 // (splat_may_touch, igs_common.cuh), 32 at a time, and only walks the survivors.
@@ -22,30 +31,23 @@
 namespace igs {
 
 
-// Sum 16 per-lane values over the warp; lane l returns the total of v[l>>1].
-__device__ __forceinline__ float warp_transpose_reduce16(const float (&v)[16], int lane) {
-  constexpr unsigned FULL = 0xffffffffu;
-  float w8[8], w4[4], w2[2];
-  const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
-#pragma unroll
-  for (int i = 0; i < 8; i++) {
-    const float send = b4 ? v[i] : v[i + 8], keep = b4 ? v[i + 8] : v[i];
-    w8[i] = keep + __shfl_xor_sync(FULL, send, 16);
-  }
-#pragma unroll
-  for (int i = 0; i < 4; i++) {
-    const float send = b3 ? w8[i] : w8[i + 4], keep = b3 ? w8[i + 4] : w8[i];
-    w4[i] = keep + __shfl_xor_sync(FULL, send, 8);
-  }
-#pragma unroll
-  for (int i = 0; i < 2; i++) {
-    const float send = b2 ? w4[i] : w4[i + 2], keep = b2 ? w4[i + 2] : w4[i];
-    w2[i] = keep + __shfl_xor_sync(FULL, send, 4);
-  }
-  const float send = b1 ? w2[0] : w2[1], keep = b1 ? w2[1] : w2[0];
-  const float w1 = keep + __shfl_xor_sync(FULL, send, 2);
-  return w1 + __shfl_xor_sync(FULL, w1, 1);
+__device__ __forceinline__ uint32_t tf32_hi(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
 }
+// D += A(16x8, row) * B(8x8, col), TF32 inputs, fp32 accumulate
+__device__ __forceinline__ void mma_tf32(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                         uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void red_add_v2(float* addr, float x, float y) {
+  asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(x), "f"(y) : "memory");
+}
+
+constexpr int PEND = 16;     // parked splats per matrix product (the M of m16n8k8)
 
 constexpr int BW = 4;        // warps per CTA: one per SM sub-partition
 constexpr int BT = BW * 32;
@@ -74,9 +76,18 @@ struct PixelBack {
 };
 
 template <int ED_T> // 0, 1, or -1 = generic
-__global__ void __launch_bounds__(BT) render_backward_kernel(BwdRenderArgs a) {
+__global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a) {
   __shared__ float4 s_rec[BW][4][32];
   __shared__ uint32_t s_id[BW][32];
+  // parked blend weights [0] and g = G*dL/dalpha [1] of up to PEND splats; pixel p of slot s sits
+  // in column p ^ ((s & 1) << 4) so that both the scalar stores and the 16-byte fragment loads are
+  // bank-conflict free
+  __shared__ __align__(16) float s_wg[BW][2][PEND][32];
+  __shared__ float4 s_pend[BW][PEND]; // {mean.x - block x0, mean.y - block y0, gaussian id bits, -}
+  // right-hand fragments, one float4 per lane: [0..1] dL_dpixel TF32 hi, [2..3] lo (per unit),
+  // and the moment basis (the same for every warp and unit)
+  __shared__ float4 s_bf[BW][4][32];
+  __shared__ float4 s_bm[2][32];
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int num_units = a.grid_x * a.grid_y * 8;
@@ -86,6 +97,28 @@ __global__ void __launch_bounds__(BT) render_backward_kernel(BwdRenderArgs a) {
   const uint32_t smine = sbase + lane * 16;
   const uint32_t sidb = (uint32_t)__cvta_generic_to_shared(&s_id[warp][0]);
   const float bg0 = __ldg(a.bg), bg1 = __ldg(a.bg + 1), bg2 = __ldg(a.bg + 2);
+  // mma fragment coordinates: this lane owns rows fg, fg+8 (splat slots) of A and C, and the
+  // k-columns ft, ft+4; k-step 2q+h of the product covers pixels 16q + 4*ft + {2h, 2h+1}
+  const int fg = lane >> 2, ft = lane & 3;
+  const uint32_t swg = (uint32_t)__cvta_generic_to_shared(&s_wg[warp][0][0][0]);
+  const uint32_t sfrag = swg + fg * 128 + ft * 16; // + (q ^ (fg & 1)) * 64: the slot's swizzle (+8 slots: +1024, g: +2048)
+  // moment basis of the pixels of this lane's k-columns, row fg of the right-hand matrix:
+  // {1, lx, lx^2, lx*ly, ly^2, ly, 0, 0}; small integers, exact in TF32
+  if (warp == 0) {
+#pragma unroll
+    for (int q = 0; q < 2; q++) {
+      float v[4];
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        const float lx = (float)(4 * (ft & 1) + i), ly = (float)(2 * q + (ft >> 1));
+        v[i] = fg == 0 ? 1.f : fg == 1 ? lx : fg == 2 ? lx * lx : fg == 3 ? lx * ly : fg == 4 ? ly * ly : fg == 5 ? ly : 0.f;
+      }
+      s_bm[q][lane] = make_float4(v[0], v[1], v[2], v[3]);
+    }
+  }
+  __syncthreads();
+  const uint32_t sbf = (uint32_t)__cvta_generic_to_shared(&s_bf[warp][0][lane]);
+  const uint32_t sbm = (uint32_t)__cvta_generic_to_shared(&s_bm[0][lane]);
 
  // persistent: every warp pulls (tile, 8x4 block) units from one ticket, heaviest tiles first
  for (;;) {
@@ -133,6 +166,87 @@ __global__ void __launch_bounds__(BT) render_backward_kernel(BwdRenderArgs a) {
     dpa = a.dL_dalpha[pix];
     if (ED >= 1) dpe0 = a.dL_dextra[pix];
   }
+  // right-hand matrix of the attribute product: dL_dpixel channel fg at this lane's k-columns,
+  // transposed through shared memory once per unit and split into TF32 hi + lo
+  {
+    float* sD = &s_wg[warp][0][0][0];
+    sD[lane] = dpc0; sD[32 + lane] = dpc1; sD[64 + lane] = dpc2; sD[96 + lane] = dpd;
+    sD[128 + lane] = dpn0; sD[160 + lane] = dpn1; sD[192 + lane] = dpn2; sD[224 + lane] = dpe0;
+    __syncwarp();
+    const float4 d0 = *reinterpret_cast<const float4*>(sD + fg * 32 + 4 * ft);
+    const float4 d1 = *reinterpret_cast<const float4*>(sD + fg * 32 + 16 + 4 * ft);
+    __syncwarp();
+    const float d[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+    float hi[8], lo[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      hi[i] = __uint_as_float(tf32_hi(d[i]));
+      lo[i] = d[i] - hi[i];
+    }
+    sts128b(sbf, make_float4(hi[0], hi[1], hi[2], hi[3]));
+    sts128b(sbf + 512, make_float4(hi[4], hi[5], hi[6], hi[7]));
+    sts128b(sbf + 1024, make_float4(lo[0], lo[1], lo[2], lo[3]));
+    sts128b(sbf + 1536, make_float4(lo[4], lo[5], lo[6], lo[7]));
+  }
+  int npend = 0;
+  // the two matrix products over the parked splats + atomics into the accumulator rows
+  auto flush = [&](const int n) {
+    __syncwarp();
+    float ca[4] = {0.f, 0.f, 0.f, 0.f}, cb[4] = {0.f, 0.f, 0.f, 0.f}, cc[4] = {0.f, 0.f, 0.f, 0.f};
+    float ma[4] = {0.f, 0.f, 0.f, 0.f}, mb[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int q = 0; q < 2; q++) {
+      const uint32_t sq = sfrag + ((q ^ (fg & 1)) << 6);
+      const float4 wA = lds128b(sq), wB = lds128b(sq + 1024);
+      const float4 gA = lds128b(sq + 2048), gB = lds128b(sq + 3072);
+      const float wv[8] = {wA.x, wB.x, wA.y, wB.y, wA.z, wB.z, wA.w, wB.w};
+      const float gv[8] = {gA.x, gB.x, gA.y, gB.y, gA.z, gB.z, gA.w, gB.w};
+      const float4 fh = lds128b(sbf + q * 512), fl = lds128b(sbf + 1024 + q * 512), fm = lds128b(sbm + q * 512);
+      const uint32_t bh[4] = {__float_as_uint(fh.x), __float_as_uint(fh.y), __float_as_uint(fh.z), __float_as_uint(fh.w)};
+      const uint32_t bl[4] = {__float_as_uint(fl.x), __float_as_uint(fl.y), __float_as_uint(fl.z), __float_as_uint(fl.w)};
+      const uint32_t bm[4] = {__float_as_uint(fm.x), __float_as_uint(fm.y), __float_as_uint(fm.z), __float_as_uint(fm.w)};
+      uint32_t wh[8], wl[8], gh[8], gl[8];
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        wh[i] = tf32_hi(wv[i]); wl[i] = __float_as_uint(wv[i] - __uint_as_float(wh[i]));
+        gh[i] = tf32_hi(gv[i]); gl[i] = __float_as_uint(gv[i] - __uint_as_float(gh[i]));
+      }
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        const int b = 2 * h, o = 4 * h;
+        mma_tf32(ca, wh[o], wh[o + 1], wh[o + 2], wh[o + 3], bh[b], bh[b + 1]);
+        mma_tf32(cb, wl[o], wl[o + 1], wl[o + 2], wl[o + 3], bh[b], bh[b + 1]);
+        mma_tf32(cc, wh[o], wh[o + 1], wh[o + 2], wh[o + 3], bl[b], bl[b + 1]);
+        mma_tf32(ma, gh[o], gh[o + 1], gh[o + 2], gh[o + 3], bm[b], bm[b + 1]);
+        mma_tf32(mb, gl[o], gl[o + 1], gl[o + 2], gl[o + 3], bm[b], bm[b + 1]);
+      }
+    }
+    const float4 pA = s_pend[warp][fg], pB = s_pend[warp][fg + 8];
+    float* rowA = a.accum + (size_t)__float_as_uint(pA.z) * ACC_F;
+    float* rowB = a.accum + (size_t)__float_as_uint(pB.z) * ACC_F;
+    const bool liveA = fg < n, liveB = fg + 8 < n;
+    // attribute gradients: C[slot][channel], this lane holds channels 2ft, 2ft+1 -> accumulator 6 + channel
+    if (liveA) red_add_v2(rowA + 6 + 2 * ft, ca[0] + cb[0] + cc[0], ca[1] + cb[1] + cc[1]);
+    if (liveB) red_add_v2(rowB + 6 + 2 * ft, ca[2] + cb[2] + cc[2], ca[3] + cb[3] + cc[3]);
+    // moments about the block origin {S0, Sx | Sxx, Sxy | Syy, Sy | 0, 0} -> about the splat
+    // centre: dx = mean.x - pixel.x = ax - lx, dy = ay - ly
+    const int l0 = lane & ~3;
+#pragma unroll
+    for (int r = 0; r < 2; r++) {
+      const float m0 = ma[2 * r] + mb[2 * r], m1 = ma[2 * r + 1] + mb[2 * r + 1];
+      const float S0 = __shfl_sync(0xffffffffu, m0, l0), Sx = __shfl_sync(0xffffffffu, m1, l0);
+      const float Sy = __shfl_sync(0xffffffffu, m1, l0 + 2);
+      const float ax = r ? pB.x : pA.x, ay = r ? pB.y : pA.y;
+      float o0, o1;
+      if (ft == 0) { o0 = fmaf(ax, S0, -Sx); o1 = fmaf(ay, S0, -Sy); }                 // sum g dx, sum g dy
+      else if (ft == 1) {                                                             // sum g dx^2, sum g dx dy
+        o0 = fmaf(ax, fmaf(ax, S0, -2.f * Sx), m0);
+        o1 = fmaf(ax, fmaf(ay, S0, -Sy), fmaf(-ay, Sx, m1));
+      } else { o0 = fmaf(ay, fmaf(ay, S0, -2.f * Sy), m0); o1 = S0; }                  // sum g dy^2, sum g
+      if (ft < 3 && (r ? liveB : liveA)) red_add_v2((r ? rowB : rowA) + 2 * ft, o0, o1);
+    }
+    __syncwarp();
+  };
   PixelBack st{T_final, 0.f, 0.f, 0.f};
   const float bg_dot = bg0 * dpc0 + bg1 * dpc1 + bg2 * dpc2;
   const float nbgT = -T_final * bg_dot;
@@ -209,20 +323,16 @@ __global__ void __launch_bounds__(BT) render_backward_kernel(BwdRenderArgs a) {
         const float dL_dalpha = fmaf(u - st.A, st.T, nbgT * rc);
         gp = G * dL_dalpha;
       }
-      // moments of gp about the splat centre: the per-Gaussian kernel turns them into
+      // park w and g; the per-Gaussian kernel turns the moments of g about the splat centre into
       // dL/dmean2D, dL/dconic and dL/dopacity (they only differ by per-Gaussian factors)
-      float v[16];
-      const float gx = gp * dx, gy = gp * dy;
-      v[0] = gx; v[1] = gy; v[2] = gx * dx; v[3] = gx * dy; v[4] = gy * dy; v[5] = gp;
-      v[6] = weight * dpc0; v[7] = weight * dpc1; v[8] = weight * dpc2; v[9] = weight * dpd;
-      v[10] = weight * dpn0; v[11] = weight * dpn1; v[12] = weight * dpn2;
-      v[13] = ED >= 1 ? weight * dpe0 : 0.f;
-      v[14] = 0.f; v[15] = 0.f;
-      const float tot = warp_transpose_reduce16(v, lane);
       uint32_t id;
       asm volatile("ld.shared.u32 %0, [%1];" : "=r"(id) : "r"(sidb + j * 4));
-      if (!(lane & 1) && (lane >> 1) < 13 + (ED >= 1 ? 1 : 0))
-        atomicAdd(a.accum + (size_t)id * ACC_F + (lane >> 1), tot);
+      {
+        const uint32_t at = swg + npend * 128 + ((uint32_t)lane ^ ((npend & 1) << 4)) * 4;
+        asm volatile("st.shared.f32 [%0], %1;" ::"r"(at), "f"(weight) : "memory");
+        asm volatile("st.shared.f32 [%0], %1;" ::"r"(at + 2048), "f"(gp) : "memory");
+        if (lane == 0) s_pend[warp][npend] = make_float4(r1.x - wx0, r1.y - wy0, __uint_as_float(id), 0.f);
+      }
       if (ED_T < 0) { // channels 1.. : plain warp reduction into the side array
         for (int c = 1; c < ED; c++) {
           float gsum = valid ? weight * a.dL_dextra[c * HW + pix] : 0.f;
@@ -231,8 +341,10 @@ __global__ void __launch_bounds__(BT) render_backward_kernel(BwdRenderArgs a) {
           if (lane == 0) atomicAdd(a.accum_extra + (size_t)id * (ED - 1) + (c - 1), gsum);
         }
       }
+      if (++npend == PEND) { flush(PEND); npend = 0; }
     }
   }
+  if (npend) flush(npend);
   __syncwarp(); // the next unit reuses this warp's shared-memory slots
  } // unit loop
 }
@@ -242,6 +354,7 @@ static int resident_ctas_bwd(K kernel, int threads) {
   int dev = 0, sms = 0, per_sm = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0);
   // 6 x 4 warps per SM measured best on B200 (sweep 2..8 in profiles/r01_v3_notes.md): fewer
   // resident warps leave a deeper ticket queue (better balance), more hide more latency

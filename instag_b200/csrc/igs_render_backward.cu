@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
   // in column p ^ ((s & 1) << 4) so that both the scalar stores and the 16-byte fragment loads are
   // bank-conflict free
   __shared__ __align__(16) float s_wg[BW][2][PEND][32];
-  __shared__ float4 s_pend[BW][PEND]; // {mean.x - block x0, mean.y - block y0, gaussian id bits, -}
+  __shared__ float4 s_pend[BW][PEND]; // {mean.x, mean.y, gaussian id bits, -}
   // right-hand fragments, one float4 per lane: [0..1] dL_dpixel TF32 hi, [2..3] lo (per unit),
   // and the moment basis (the same for every warp and unit)
   __shared__ float4 s_bf[BW][4][32];
@@ -119,6 +119,7 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
   __syncthreads();
   const uint32_t sbf = (uint32_t)__cvta_generic_to_shared(&s_bf[warp][0][lane]);
   const uint32_t sbm = (uint32_t)__cvta_generic_to_shared(&s_bm[0][lane]);
+  const uint32_t spend = (uint32_t)__cvta_generic_to_shared(&s_pend[warp][0]);
 
  // persistent: every warp pulls (tile, 8x4 block) units from one ticket, heaviest tiles first
  for (;;) {
@@ -188,7 +189,6 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
     sts128b(sbf + 1024, make_float4(lo[0], lo[1], lo[2], lo[3]));
     sts128b(sbf + 1536, make_float4(lo[4], lo[5], lo[6], lo[7]));
   }
-  int npend = 0;
   // the two matrix products over the parked splats + atomics into the accumulator rows
   auto flush = [&](const int n) {
     __syncwarp();
@@ -236,7 +236,7 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
       const float m0 = ma[2 * r] + mb[2 * r], m1 = ma[2 * r + 1] + mb[2 * r + 1];
       const float S0 = __shfl_sync(0xffffffffu, m0, l0), Sx = __shfl_sync(0xffffffffu, m1, l0);
       const float Sy = __shfl_sync(0xffffffffu, m1, l0 + 2);
-      const float ax = r ? pB.x : pA.x, ay = r ? pB.y : pA.y;
+      const float ax = (r ? pB.x : pA.x) - wx0, ay = (r ? pB.y : pA.y) - wy0;
       float o0, o1;
       if (ft == 0) { o0 = fmaf(ax, S0, -Sx); o1 = fmaf(ay, S0, -Sy); }                 // sum g dx, sum g dy
       else if (ft == 1) {                                                             // sum g dx^2, sum g dx dy
@@ -250,6 +250,54 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
   PixelBack st{T_final, 0.f, 0.f, 0.f};
   const float bg_dot = bg0 * dpc0 + bg1 * dpc1 + bg2 * dpc2;
   const float nbgT = -T_final * bg_dot;
+
+  uint32_t park_at = swg + lane * 4, pend_at = spend; // this lane's word of the next free slot; its info record
+  // one splat some pixel of the warp blends: per-pixel recurrences, then park w and g
+  auto blend = [&](const int j, const float4 r1, const float G, const float alpha, const bool valid) {
+    float weight = 0.f, gp = 0.f; // alpha*T ; G * dL/dalpha; lanes that do not blend park exact zeros
+    if (valid) {
+      const float4 r2 = lds128b(sbase + 1024 + j * 16);
+      const float4 r3 = lds128b(sbase + 1536 + j * 16);
+      const float rc = rcp_approx(__fsub_rn(1.f, alpha));
+      st.T = st.T * rc;                              // reference backward.cu:612 (T / (1 - alpha))
+      weight = alpha * st.T;
+      float u = fmaf(r2.x, dpc0, dpa), u2 = r2.y * dpc1;
+      u = fmaf(r2.z, dpc2, u); u2 = fmaf(r1.z, dpd, u2);
+      u = fmaf(r2.w, dpn0, u); u2 = fmaf(r3.x, dpn1, u2);
+      u = fmaf(r3.y, dpn2, u);
+      if (ED >= 1) u2 = fmaf(r1.w, dpe0, u2);
+      u += u2;
+      if (ED_T < 0) {
+        uint32_t gid;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(gid) : "r"(sidb + j * 4));
+        const float* e = a.extra_attrs + (size_t)gid * ED;
+        for (int c = 1; c < ED; c++) u = fmaf(__ldg(e + c), a.dL_dextra[c * HW + pix], u);
+      }
+      st.A = fmaf(st.last_alpha, st.u_last - st.A, st.A);
+      st.u_last = u;
+      st.last_alpha = alpha;
+      // + background term, reference backward.cu:684-687
+      const float dL_dalpha = fmaf(u - st.A, st.T, nbgT * rc);
+      gp = G * dL_dalpha;
+    }
+    // the per-Gaussian kernel turns the moments of g about the splat centre into dL/dmean2D,
+    // dL/dconic and dL/dopacity (they only differ by per-Gaussian factors)
+    uint32_t id;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(id) : "r"(sidb + j * 4));
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(park_at), "f"(weight) : "memory");
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(park_at + 2048), "f"(gp) : "memory");
+    if (lane == 0) sts128b(pend_at, make_float4(r1.x, r1.y, __uint_as_float(id), 0.f));
+    park_at = (park_at + 128) ^ 64; // next slot, its column swizzle toggles
+    pend_at += 16;
+    if (ED_T < 0) { // channels 1.. : plain warp reduction into the side array
+      for (int c = 1; c < ED; c++) {
+        float gsum = valid ? weight * a.dL_dextra[c * HW + pix] : 0.f;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) gsum += __shfl_xor_sync(0xffffffffu, gsum, o);
+        if (lane == 0) atomicAdd(a.accum_extra + (size_t)id * (ED - 1) + (c - 1), gsum);
+      }
+    }
+  };
 
   // entry e of the reverse walk is list position wmax-1-e (= its `contributor` index)
   const uint32_t* __restrict__ list = a.point_list + range.x;
@@ -287,64 +335,34 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
       s_id[warp][lane] = id_mine;
     }
     __syncwarp();
+    const int jmin = wmax - 1 - cb - last_contributor; // entry j is in front of this pixel's last contributor iff j > jmin
+    // two staged splats per trip: the two alpha evaluations are independent, the recurrences run in order
     while (m) {
-      const int j = __ffs(m) - 1;
+      const int j0 = __ffs(m) - 1;
       m &= m - 1;
-      const int contributor = wmax - 1 - cb - j;
-      const float4 r1 = lds128b(sbase + 512 + j * 16);
-      const float4 r0 = lds128b(sbase + j * 16);
-      const float dx = __fsub_rn(r1.x, pxf), dy = __fsub_rn(r1.y, pyf);
-      const float power = gauss_power(r0.x, r0.y, r0.z, dx, dy);
-      const float G = expf(power);
-      const float alpha = fminf(0.99f, __fmul_rn(r0.w, G));
-      const bool valid = contributor < last_contributor && !(power > 0.0f) && !(alpha < ALPHA_MIN);
-      if (!__any_sync(0xffffffffu, valid)) continue;
-      // per-pixel partials; lanes that do not blend this splat contribute exact zeros
-      float weight = 0.f, gp = 0.f; // alpha*T ; G * dL/dalpha
-      if (valid) {
-        const float4 r2 = lds128b(sbase + 1024 + j * 16);
-        const float4 r3 = lds128b(sbase + 1536 + j * 16);
-        const float rc = rcp_approx(__fsub_rn(1.f, alpha));
-        st.T = st.T * rc;                              // reference backward.cu:612 (T / (1 - alpha))
-        weight = alpha * st.T;
-        float u = dpa;
-        u = fmaf(r2.x, dpc0, u); u = fmaf(r2.y, dpc1, u); u = fmaf(r2.z, dpc2, u);
-        u = fmaf(r1.z, dpd, u);
-        u = fmaf(r2.w, dpn0, u); u = fmaf(r3.x, dpn1, u); u = fmaf(r3.y, dpn2, u);
-        if (ED >= 1) u = fmaf(r1.w, dpe0, u);
-        if (ED_T < 0) {
-          const float* e = a.extra_attrs + (size_t)s_id[warp][j] * ED;
-          for (int c = 1; c < ED; c++) u = fmaf(__ldg(e + c), a.dL_dextra[c * HW + pix], u);
-        }
-        st.A = fmaf(st.last_alpha, st.u_last - st.A, st.A);
-        st.u_last = u;
-        st.last_alpha = alpha;
-        // + background term, reference backward.cu:684-687
-        const float dL_dalpha = fmaf(u - st.A, st.T, nbgT * rc);
-        gp = G * dL_dalpha;
+      const bool two = m != 0;
+      const int j1 = two ? __ffs(m) - 1 : j0;
+      m &= m - 1;
+      const float4 a1 = lds128b(sbase + 512 + j0 * 16), a0 = lds128b(sbase + j0 * 16);
+      const float4 b1 = lds128b(sbase + 512 + j1 * 16), b0 = lds128b(sbase + j1 * 16);
+      const float dxa = __fsub_rn(a1.x, pxf), dya = __fsub_rn(a1.y, pyf);
+      const float dxb = __fsub_rn(b1.x, pxf), dyb = __fsub_rn(b1.y, pyf);
+      const float pa = gauss_power(a0.x, a0.y, a0.z, dxa, dya), pb = gauss_power(b0.x, b0.y, b0.z, dxb, dyb);
+      const float Ga = expf(pa), Gb = expf(pb);
+      const float ala = fminf(0.99f, __fmul_rn(a0.w, Ga)), alb = fminf(0.99f, __fmul_rn(b0.w, Gb));
+      const bool va = j0 > jmin && !(pa > 0.0f) && !(ala < ALPHA_MIN);
+      const bool vb = two && j1 > jmin && !(pb > 0.0f) && !(alb < ALPHA_MIN);
+      const bool anya = __any_sync(0xffffffffu, va), anyb = __any_sync(0xffffffffu, vb);
+      if (anya) blend(j0, a1, Ga, ala, va);
+      if (anyb) blend(j1, b1, Gb, alb, vb);
+      if (pend_at >= spend + (PEND - 1) * 16) { // the next trip may park two more
+        flush((int)(pend_at - spend) >> 4);
+        park_at = swg + lane * 4;
+        pend_at = spend;
       }
-      // park w and g; the per-Gaussian kernel turns the moments of g about the splat centre into
-      // dL/dmean2D, dL/dconic and dL/dopacity (they only differ by per-Gaussian factors)
-      uint32_t id;
-      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(id) : "r"(sidb + j * 4));
-      {
-        const uint32_t at = swg + npend * 128 + ((uint32_t)lane ^ ((npend & 1) << 4)) * 4;
-        asm volatile("st.shared.f32 [%0], %1;" ::"r"(at), "f"(weight) : "memory");
-        asm volatile("st.shared.f32 [%0], %1;" ::"r"(at + 2048), "f"(gp) : "memory");
-        if (lane == 0) s_pend[warp][npend] = make_float4(r1.x - wx0, r1.y - wy0, __uint_as_float(id), 0.f);
-      }
-      if (ED_T < 0) { // channels 1.. : plain warp reduction into the side array
-        for (int c = 1; c < ED; c++) {
-          float gsum = valid ? weight * a.dL_dextra[c * HW + pix] : 0.f;
-#pragma unroll
-          for (int o = 16; o > 0; o >>= 1) gsum += __shfl_xor_sync(0xffffffffu, gsum, o);
-          if (lane == 0) atomicAdd(a.accum_extra + (size_t)id * (ED - 1) + (c - 1), gsum);
-        }
-      }
-      if (++npend == PEND) { flush(PEND); npend = 0; }
     }
   }
-  if (npend) flush(npend);
+  if (pend_at != spend) flush((int)(pend_at - spend) >> 4);
   __syncwarp(); // the next unit reuses this warp's shared-memory slots
  } // unit loop
 }

@@ -25,6 +25,10 @@ SCENES = {
     "sh0_m9_noextra": dict(P=1000, W=48, H=64, sh_degree=0, M=9, ED=0, scale_mult=2.0, seed=4),
     "big_splats_ed3": dict(P=300, W=64, H=64, sh_degree=2, M=9, ED=3, scale_mult=12.0, seed=5),
     "dense_450": dict(P=20000, W=450, H=450, sh_degree=None, ED=1, scale_mult=1.5, seed=6),
+    # lists of several thousand entries per tile: the backward restarts from the forward's
+    # checkpoints every 256 entries (list segments, igs_common.cuh)
+    "long_lists": dict(P=40000, W=64, H=48, sh_degree=None, ED=1, scale_mult=0.6, seed=9),
+    "long_lists_sh_noextra": dict(P=25000, W=40, H=64, sh_degree=1, M=4, ED=0, scale_mult=0.8, seed=10),
     "one_gaussian": dict(P=1, W=32, H=32, sh_degree=None, ED=1, scale_mult=0.05, seed=7),
     "wide_cloud_culled": dict(P=5000, W=160, H=120, sh_degree=1, M=4, ED=1, scale_mult=3.0, seed=8, extent=1.2),
 }
@@ -36,7 +40,7 @@ def _need_ref():
         pytest.skip("oracle/_ref/libdgr_ref.so not built (needs /root/reference at build time)")
 
 
-def _check_against(ours, theirs, sc, exact_geom=True, floor=0.0, border=None):
+def _check_against(ours, theirs, sc, exact_geom=True, floor=0.0, border=None, grad_rtol=None):
     assert int(ours["num_rendered"]) == int(theirs["num_rendered"])
     if sc["means3D"].shape[0] == 0:
         return
@@ -61,7 +65,7 @@ def _check_against(ours, theirs, sc, exact_geom=True, floor=0.0, border=None):
         mask = ~same
     U.assert_forward_close(ours, theirs, mask=mask)
     if "dL_dmeans3D" in theirs and (mask is None or not mask.any()):
-        U.assert_grads_close(ours, theirs, rtol=max(U.GRAD_RTOL, 4 * floor))
+        U.assert_grads_close(ours, theirs, rtol=grad_rtol or max(U.GRAD_RTOL, 4 * floor))
 
 
 @pytest.mark.parametrize("name", sorted(SCENES))
@@ -84,7 +88,11 @@ def test_against_cpu_oracle(name):
     g = S.upstream_grads(sc["H"], sc["W"], extra_dims=kw.get("ED", 1), seed=11)
     o = U.run_oracle(sc, grads=g)
     ours = U.run_igs(sc, grads=g)
-    _check_against(ours, o, sc, exact_geom=True, border=o["borderline"].astype(bool))
+    # lists of thousands of entries: the CPU oracle's libm expf differs from CUDA's expf in the last
+    # bit and the difference compounds along T; against the reference CUDA rasterizer (same expf)
+    # these scenes are held to 1e-4 above
+    rtol = 3e-4 if name.startswith("long_lists") else None
+    _check_against(ours, o, sc, exact_geom=True, border=o["borderline"].astype(bool), grad_rtol=rtol)
 
 
 @pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz"))))

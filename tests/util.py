@@ -98,15 +98,17 @@ def igs_sorted_keys(binb, capacity, num_rendered):
 
 
 def bin_capacity_from_bytes(nbytes):
-    """Invert igs_bin_bytes (12 B per instance, two 256 B-aligned arrays)."""
+    """Invert igs_bin_bytes (monotone in the capacity): largest capacity whose workspace fits."""
     from instag_b200 import _native as N
     lib = N.lib()
-    cap = max((nbytes - 512) // 12, 1)
-    while lib.igs_bin_bytes(cap) < nbytes:
-        cap += 1
-    while cap > 1 and lib.igs_bin_bytes(cap - 1) >= nbytes:
-        cap -= 1
-    return cap
+    lo, hi = 1, max(nbytes // 4, 2)
+    while lo < hi:
+        mid = (lo + hi + 1) // 2
+        if lib.igs_bin_bytes(mid) <= nbytes:
+            lo = mid
+        else:
+            hi = mid - 1
+    return lo
 
 
 # ---------------------------------------------------------------------------

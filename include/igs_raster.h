@@ -200,6 +200,45 @@ int igs_debug_trace(void* device_buffer);
 int igs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
                      const float* projmatrix, uint8_t* present, igs_stream_t stream);
 
+/* ---- the steps either side of the rasterizer call ------------------------
+ *
+ * f1  igs_compose_frame replaces the per-frame tensor expression of the synthesis loop,
+ *     /root/reference/synthesize_fuse.py:64-76:
+ *         alpha_mouth = dilate_fn(alpha_mouth)                      (only with dilate_ksize > 0; :19-22, k = 13)
+ *         mouth_image = mouth_rgb + background / 255 * (1 - alpha_mouth)
+ *         image       = face_rgb + mouth_image * (1 - face_alpha)
+ *         pred        = (clamp(image, 0, 1) * 255).astype(uint8), HWC
+ *     rgb planes [3,H,W], alpha planes [1,H,W], background [3,H,W] in 0..255 or NULL (black);
+ *     out_u8 [H,W,3]; out_image [3,H,W] (the un-clamped `image`) or NULL.  The frame stays on
+ *     the device: the caller copies ring slots to pinned memory asynchronously
+ *     (instag_b200/synthesis.py) instead of the reference's blocking .cpu() per frame.
+ *
+ * f2  igs_activate_forward / _backward replace gaussian_renderer/__init__.py:227-235
+ *         means3D   = xyz + d_xyz
+ *         scales    = softplus(_scaling + d_scale)      (scene/gaussian_model.py:43)
+ *         rotations = normalize(_rotation + d_rot)      (:51, eps 1e-12)
+ *         opacity   = sigmoid(_opacity)                 (:48)
+ *     and their autograd backward; d_* and upstream gradients may be NULL (zero).  The
+ *     gradient of a d_* input equals the gradient of its parameter.
+ *     igs_densify_stats replaces train_face.py:675-682 + scene/gaussian_model.py:683-685, in
+ *     place, for the Gaussians with radii > 0:
+ *         max_radii2D = max(max_radii2D, radii);  xyz_gradient_accum += |grad_means2D[:, :2]|;  denom += 1
+ *     grad_means2D is [P,3]; max_radii2D, xyz_gradient_accum, denom are [P] / [P,1] float. */
+int igs_compose_frame(const float* face_rgb, const float* face_alpha, const float* mouth_rgb,
+                      const float* mouth_alpha, const float* background, int32_t H, int32_t W,
+                      int32_t dilate_ksize, uint8_t* out_u8, float* out_image, igs_stream_t stream);
+int igs_activate_forward(int32_t P, const float* xyz, const float* d_xyz, const float* scaling,
+                         const float* d_scale, const float* rotation, const float* d_rot,
+                         const float* opacity, float* means3D, float* scales, float* rotations,
+                         float* opacities, igs_stream_t stream);
+int igs_activate_backward(int32_t P, const float* scaling, const float* d_scale, const float* rotation,
+                          const float* d_rot, const float* opacity, const float* g_means3D,
+                          const float* g_scales, const float* g_rotations, const float* g_opacities,
+                          float* g_xyz, float* g_scaling, float* g_rotation, float* g_opacity,
+                          igs_stream_t stream);
+int igs_densify_stats(int32_t P, const int32_t* radii, const float* grad_means2D, float* max_radii2D,
+                      float* xyz_gradient_accum, float* denom, igs_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -73,6 +73,10 @@ SYMBOLS = {
     "igs_launch_count": (C.c_uint64, []),
     "igs_debug_trace": (C.c_int, [_p]),
     "igs_mark_visible": (C.c_int, [C.c_int32, _p, _p, _p, _p, _p]),
+    "igs_compose_frame": (C.c_int, [_p, _p, _p, _p, _p, C.c_int32, C.c_int32, C.c_int32, _p, _p, _p]),
+    "igs_activate_forward": (C.c_int, [C.c_int32] + [_p] * 12),
+    "igs_activate_backward": (C.c_int, [C.c_int32] + [_p] * 14),
+    "igs_densify_stats": (C.c_int, [C.c_int32] + [_p] * 6),
 }
 
 _lib = None

@@ -1,0 +1,145 @@
+"""Frame-sharded synthesis driver around the rasterizer.
+
+Mirrors the per-frame body of the reference's `render_set` (synthesize_fuse.py:53-90): the
+caller still produces the face and mouth render packages with its own `render_motion*`
+functions (which call `diff_gauss`, i.e. this library); what changes is everything after them:
+
+* `compose_frame` -- ONE kernel (`igs_compose_frame`) for the optional dilation of the mouth
+  alpha, mouth-over-background, face-over-mouth, clamp, *255 and the uint8 HWC conversion
+  (reference: ~12 element-wise launches and three full-frame temporaries per frame);
+* `FrameRing` -- the uint8 frame is written into a device ring slot and copied to pinned host
+  memory on a side stream; the reference blocks on `.cpu().numpy()` every frame
+  (synthesize_fuse.py:76), which serialises rendering and the PCIe copy;
+* `synthesize_sequence` -- the frames of a sequence are independent (read-only models, one
+  camera/audio window per frame), so rank r of world renders frames r, r+world, ...; there is
+  no collective on the render path.
+
+No CPU fallback: CUDA tensors only.
+"""
+import numpy as np
+import torch
+
+from . import _native as N
+from .sharding import shard_indices
+
+
+def _f32(t):
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def compose_frame(face_render, face_alpha, mouth_render, mouth_alpha, background=None, dilate=False,
+                  ksize=13, out=None, out_image=None):
+    """pred = uint8 HWC frame of synthesize_fuse.py:64-76.
+
+    face_render / mouth_render [3,H,W], face_alpha / mouth_alpha [1,H,W] (the `render` and `alpha`
+    entries of the two render packages), background = `view.background` ([3,H,W], 0..255) or None.
+    out: optional uint8 [H,W,3] CUDA tensor (e.g. a FrameRing slot); out_image: optional float32
+    [3,H,W] receiving the un-clamped `image`."""
+    if not face_render.is_cuda:
+        raise RuntimeError("libigs_raster is CUDA-only: compose_frame needs CUDA tensors (no CPU fallback)")
+    H, W = int(face_render.shape[-2]), int(face_render.shape[-1])
+    dev = face_render.device
+    keep = [_f32(face_render[0:3]), _f32(face_alpha), _f32(mouth_render[0:3]), _f32(mouth_alpha),
+            None if background is None else _f32(background.to(dev))]
+    if out is None:
+        out = torch.empty((H, W, 3), dtype=torch.uint8, device=dev)
+    if tuple(out.shape) != (H, W, 3) or out.dtype != torch.uint8 or not out.is_contiguous():
+        raise ValueError("out must be a contiguous uint8 [H,W,3] tensor")
+    ptr = lambda t: None if t is None else t.data_ptr()
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    with torch.cuda.device(dev):
+        N.check(N.lib().igs_compose_frame(ptr(keep[0]), ptr(keep[1]), ptr(keep[2]), ptr(keep[3]), ptr(keep[4]), H, W,
+                                          int(ksize) if dilate else 0, out.data_ptr(), ptr(out_image), stream),
+                "compose_frame")
+    return out
+
+
+class FrameRing:
+    """`depth` uint8 [H,W,3] slots on the device, mirrored in pinned host memory.  `slot()` hands
+    out the next device slot (waiting only if its previous copy has not finished); `commit()`
+    queues the device->host copy on a side stream; `collect()` returns finished frames in order."""
+
+    def __init__(self, H, W, depth=8, device=None):
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.dev = torch.empty((depth, H, W, 3), dtype=torch.uint8, device=self.device)
+        self.host = torch.empty((depth, H, W, 3), dtype=torch.uint8).pin_memory()
+        self.copy_stream = torch.cuda.Stream(self.device)
+        self.rendered = [torch.cuda.Event() for _ in range(depth)]
+        self.copied = [torch.cuda.Event() for _ in range(depth)]
+        self.depth, self.head, self.tail = depth, 0, 0  # frames committed / collected
+        self.tags = [None] * depth
+
+    def slot(self):
+        if self.head - self.tail >= self.depth:
+            raise RuntimeError("FrameRing is full: collect() before asking for another slot")
+        return self.dev[self.head % self.depth]
+
+    def commit(self, tag=None):
+        i = self.head % self.depth
+        cur = torch.cuda.current_stream(self.device)
+        self.rendered[i].record(cur)
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(self.rendered[i])
+            self.host[i].copy_(self.dev[i], non_blocking=True)
+            self.copied[i].record(self.copy_stream)
+        self.tags[i] = tag
+        self.head += 1
+
+    def collect(self, block=False):
+        """[(tag, uint8 numpy [H,W,3])] of the frames whose copy has finished, oldest first (all
+        outstanding frames with block=True).  The arrays are copies: the slot is free afterwards."""
+        out = []
+        while self.tail < self.head:
+            i = self.tail % self.depth
+            if block:
+                self.copied[i].synchronize()
+            elif not self.copied[i].query():
+                break
+            out.append((self.tags[i], self.host[i].numpy().copy()))
+            self.tail += 1
+        return out
+
+    def full(self):
+        return self.head - self.tail >= self.depth
+
+
+def synthesize_sequence(views, render_face, render_mouth, dilate=False, rank=0, world=1, ring_depth=8,
+                        sink=None):
+    """The loop of `render_set` (synthesize_fuse.py:53-78) for this rank's frames.
+
+    views: the sequence's cameras; render_face(view) / render_mouth(view) -> dicts with "render"
+    [3,H,W] and "alpha" [1,H,W] (what render_motion / render_motion_mouth_con return);
+    `view.background` is used when the view has one.  Frames idx = rank, rank+world, ... are
+    rendered; each is handed to sink(idx, uint8 HWC numpy) in order, or collected and returned as
+    (indices, uint8 array [n_local,H,W,3]) when sink is None."""
+    mine = shard_indices(len(views), rank, world)
+    ring, frames, got = None, [], []
+
+    def drain(block):
+        for tag, fr in ring.collect(block=block):
+            if sink is not None:
+                sink(tag, fr)
+            else:
+                got.append(tag)
+                frames.append(fr)
+
+    with torch.no_grad():
+        for idx in mine:
+            view = views[idx]
+            face, mouth = render_face(view), render_mouth(view)
+            H, W = face["render"].shape[-2:]
+            if ring is None:
+                ring = FrameRing(int(H), int(W), depth=ring_depth, device=face["render"].device)
+            if ring.full():
+                drain(block=True)
+            compose_frame(face["render"], face["alpha"], mouth["render"], mouth["alpha"],
+                          getattr(view, "background", None), dilate=dilate, out=ring.slot())
+            ring.commit(idx)
+            drain(block=False)
+    if ring is not None:
+        drain(block=True)
+    if sink is not None:
+        return mine, None
+    return got, (np.stack(frames) if frames else np.zeros((0, 0, 0, 3), np.uint8))

@@ -1,0 +1,85 @@
+"""Golden vectors for the SURVEY 8(f) rows f1/f2, made by evaluating the REFERENCE'S OWN torch
+expressions on CPU (this container; torch CPU ops, no reference import needed because the lines
+are plain tensor expressions -- each is quoted with its file:line).
+
+    python tests/golden/make_adjacent_golden.py      # writes tests/golden/adjacent_*.npz
+"""
+import os
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def dilate_fn(bin_img, ksize=13):  # synthesize_fuse.py:19-22
+    pad = (ksize - 1) // 2
+    return F.max_pool2d(bin_img, kernel_size=ksize, stride=1, padding=pad)
+
+
+def compose_case(H, W, seed, dilate):
+    g = torch.Generator().manual_seed(seed)
+    face = torch.rand((3, H, W), generator=g) * 1.2 - 0.1
+    fa = torch.rand((1, H, W), generator=g)
+    mouth = torch.rand((3, H, W), generator=g) * 1.1
+    ma = (torch.rand((1, H, W), generator=g) > 0.7).float() * torch.rand((1, H, W), generator=g)
+    bgimg = torch.randint(0, 256, (3, H, W), generator=g).float()
+    alpha_mouth = ma
+    if dilate:
+        alpha_mouth = dilate_fn(alpha_mouth[None])[0]                       # :66-68
+    mouth_image = mouth + bgimg / 255.0 * (1.0 - alpha_mouth)               # :70
+    image = face + mouth_image * (1.0 - fa)                                 # :74
+    pred = (image[0:3, ...].clamp(0, 1).permute(1, 2, 0).detach().cpu().numpy() * 255).astype(np.uint8)  # :76
+    return dict(face=face.numpy(), face_alpha=fa.numpy(), mouth=mouth.numpy(), mouth_alpha=ma.numpy(),
+                background=bgimg.numpy(), dilate=np.int32(13 if dilate else 0), pred=pred, image=image.numpy())
+
+
+def activate_case(P, seed):
+    g = torch.Generator().manual_seed(seed)
+    r = lambda *s: torch.randn(*s, generator=g)
+    xyz, d_xyz = r(P, 3), 0.01 * r(P, 3)
+    scaling, d_scale = 3 * r(P, 3) - 2, 0.1 * r(P, 3)
+    scaling[0] = 25.0  # softplus threshold branch
+    rotation, d_rot = r(P, 4), 0.1 * r(P, 4)
+    opacity = 2 * r(P, 1)
+    leaves = [t.clone().requires_grad_(True) for t in (xyz, d_xyz, scaling, d_scale, rotation, d_rot, opacity)]
+    x, dx, s, ds, q, dq, o = leaves
+    means3D = x + dx                                                        # gaussian_renderer/__init__.py:227
+    opac = torch.sigmoid(o)                                                 # :230 (get_opacity, gaussian_model.py:48,194)
+    scales = F.softplus(s + ds)                                             # :234 (gaussian_model.py:43)
+    rotations = F.normalize(q + dq)                                         # :235 (gaussian_model.py:51)
+    ups = [r(P, 3), r(P, 3), r(P, 4), r(P, 1)]
+    (means3D * ups[0]).sum().add((scales * ups[1]).sum()).add((rotations * ups[2]).sum()).add((opac * ups[3]).sum()).backward()
+    out = dict(xyz=xyz, d_xyz=d_xyz, scaling=scaling, d_scale=d_scale, rotation=rotation, d_rot=d_rot, opacity=opacity,
+               means3D=means3D, scales=scales, rotations=rotations, opacities=opac,
+               up_means3D=ups[0], up_scales=ups[1], up_rotations=ups[2], up_opacities=ups[3],
+               g_xyz=x.grad, g_d_xyz=dx.grad, g_scaling=s.grad, g_d_scale=ds.grad, g_rotation=q.grad, g_d_rot=dq.grad,
+               g_opacity=o.grad)
+    return {k: v.detach().numpy() for k, v in out.items()}
+
+
+def densify_case(P, seed):
+    g = torch.Generator().manual_seed(seed)
+    radii = torch.randint(-2, 30, (P,), generator=g).clamp(min=0).int()
+    grad = torch.randn(P, 3, generator=g)
+    max_radii2D = torch.rand(P, generator=g) * 20
+    xyz_gradient_accum = torch.rand(P, 1, generator=g)
+    denom = torch.randint(0, 5, (P, 1), generator=g).float()
+    before = dict(radii=radii.numpy(), grad=grad.numpy(), max_radii2D=max_radii2D.numpy().copy(),
+                  xyz_gradient_accum=xyz_gradient_accum.numpy().copy(), denom=denom.numpy().copy())
+    visibility_filter = radii > 0                                            # gaussian_renderer/__init__.py:131
+    max_radii2D[visibility_filter] = torch.max(max_radii2D[visibility_filter], radii[visibility_filter])  # train_face.py:675
+    xyz_gradient_accum[visibility_filter] += torch.norm(grad[visibility_filter, :2], dim=-1, keepdim=True)  # gaussian_model.py:684
+    denom[visibility_filter] += 1                                            # gaussian_model.py:685
+    before.update(out_max_radii2D=max_radii2D.numpy(), out_xyz_gradient_accum=xyz_gradient_accum.numpy(),
+                  out_denom=denom.numpy())
+    return before
+
+
+if __name__ == "__main__":
+    np.savez_compressed(os.path.join(HERE, "adjacent_compose_plain.npz"), **compose_case(37, 53, 1, False))
+    np.savez_compressed(os.path.join(HERE, "adjacent_compose_dilate.npz"), **compose_case(48, 40, 2, True))
+    np.savez_compressed(os.path.join(HERE, "adjacent_activate.npz"), **activate_case(257, 3))
+    np.savez_compressed(os.path.join(HERE, "adjacent_densify.npz"), **densify_case(300, 4))
+    print("written")

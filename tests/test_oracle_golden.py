@@ -12,7 +12,8 @@ import util as U
 from instag_b200 import synthetic as S
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-FILES = sorted(glob.glob(os.path.join(GOLDEN, "*.npz")))
+FILES = sorted(f for f in glob.glob(os.path.join(GOLDEN, "*.npz"))
+               if not os.path.basename(f).startswith("adjacent_"))  # those: test_adjacent_oracle.py
 
 
 def _cases():

@@ -93,6 +93,29 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
+def ncu_traffic(stage):
+    """DRAM bytes per launch of `stage`'s kernel from the newest committed ncu --set full summary
+    (profiles/rNN_vN_full.md, written by profiles/summarize.py); None if there is none."""
+    import glob
+    import re
+    kern = {"preprocess": "preprocess_kernel", "duplicate": "duplicate_kernel", "sort": "tile_sort_kernel",
+            "render": "render_kernel", "render_backward": "render_backward_kernel",
+            "preprocess_backward": "preprocess_backward_kernel"}.get(stage)
+    files = sorted(f for f in glob.glob(os.path.join(ROOT, "profiles", "r*_full.md")) if "_C5" not in f)
+    if not kern or not files:
+        return None
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    total, inside = None, False
+    for ln in open(files[-1]):
+        if ln.startswith("###"):
+            inside = kern + "<" in ln or kern + "(" in ln
+        elif inside:
+            m = re.match(r"- dram__bytes_(read|write)\.sum: ([0-9.]+) (\w+)", ln)
+            if m:
+                total = (total or 0.0) + float(m.group(2)) * unit.get(m.group(3), 1.0)
+    return total
+
+
 def algorithmic_bytes(P, N, HW, T, S=0, c=0, ED=1):
     """Per-stage algorithmic bytes with this library's record sizes (DESIGN.md "Kernels"):
     preprocess reads 44(+12S) B and writes the 64 B splat record + radii/tiles/offsets (+1 clamp),
@@ -397,7 +420,10 @@ def finish(a, cfg, sc, grads, arm, world, rank, ms, per, wall, value, e2e, clock
         dom = max(table, key=lambda k: table[k]["ms"])
         d = table[dom]
         line["roofline"] = {"kernel": dom, "bound": "hbm", "achieved": d["gbs"], "peak": hbm_peak, "unit": "GB/s",
-                            "frac": d["frac_hbm"], "traffic": None, "peak_source": peak_src,
+                            "frac": d["frac_hbm"], "traffic": ncu_traffic(dom) if a.workload == "C2" else None,
+                            "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of the newest committed "
+                                              "profiles/r*_full.md (ncu --set full of this command), bytes per launch",
+                            "peak_source": peak_src,
                             "alg_bytes_per_launch": d["alg_bytes"], "ms_per_launch": d["ms"],
                             "frames_averaged": frames,
                             "share_of_step": d["ms"] / sum(v["ms"] for v in table.values()),

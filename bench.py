@@ -39,6 +39,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-synth", action="store_true", help="skip the auxiliary forward-only synthesis fps")
+    ap.add_argument("--cloud", default=None, help="a GaussianModel .ply (save_ply format) to rasterize instead of the "
+                                                   "synthetic cloud of --workload (image size and camera stay)")
     return ap.parse_args()
 
 
@@ -297,6 +299,9 @@ def main():
 
     cfg = dict(S.CONFIGS[a.workload])
     cloud = S.make_cloud(cfg["P"], sh_degree=cfg["sh_degree"], M=cfg["M"] or None, seed=0)
+    if a.cloud:
+        cloud = cloud_from_ply(a.cloud)
+        cfg["P"], cfg["sh_degree"], cfg["M"] = cloud["means3D"].shape[0], cloud["sh_degree"], cloud["shs"].shape[1]
     cams = S.camera_sequence(max(eff_world, 1), cfg["W"], cfg["H"], seed=0)
     cam = S.make_camera(cfg["W"], cfg["H"]) if eff_world == 1 else cams[rank]
     sc = dict(cloud)
@@ -454,6 +459,19 @@ def finish(a, cfg, sc, grads, arm, world, rank, ms, per, wall, value, e2e, clock
     if not a.no_synth and a.workload == "C2":
         line["synth"] = synth_fps(torch, dist, world, rank, flush, arm.device)
     return line
+
+
+def cloud_from_ply(path):
+    """A trained head in the reference's save_ply format (instag_b200/assets.py) as a bench cloud:
+    raw parameters activated as gaussian_renderer/__init__.py:227-235 does (host side, once)."""
+    from instag_b200 import assets as AS
+    from oracle import adjacent as A  # numpy activations; set-up only, outside every timed region
+    g = AS.read_gaussian_ply(path)
+    means3D, scales, rotations, opac = A.activate(g["xyz"], None, g["scaling"], None, g["rotation"], None, g["opacity"])
+    shs = np.ascontiguousarray(np.concatenate([g["features_dc"], g["features_rest"]], axis=1), np.float32)
+    return dict(means3D=means3D, scales=scales, rotations=rotations, opacities=opac.reshape(-1, 1),
+                extra_attrs=np.ones((means3D.shape[0], 1), np.float32), shs=shs, colors_precomp=None,
+                sh_degree=g["sh_degree"])
 
 
 def synth_fps(torch, dist, world, rank, flush, device, frames=60):

@@ -239,6 +239,22 @@ int igs_activate_backward(int32_t P, const float* scaling, const float* d_scale,
 int igs_densify_stats(int32_t P, const int32_t* radii, const float* grad_means2D, float* max_radii2D,
                       float* xyz_gradient_accum, float* denom, igs_stream_t stream);
 
+/* f3  igs_l1_ssim_* replace the photometric loss on the rasterizer's colour output,
+ *         Ll1 = l1_loss(image, gt);  loss = Ll1 + lambda_dssim * (1.0 - ssim(image, gt))
+ *     (/root/reference/train_face.py:421-422, utils/loss_utils.py:28-73: 11x11 Gaussian window,
+ *     sigma 1.5, zero padding, C1 = 0.01^2, C2 = 0.03^2), and its autograd backward, which yields
+ *     the dL_dcolor image igs_backward consumes.  img1 = image, img2 = gt, both [C,H,W].
+ *     forward : writes the derivative maps dA, dB, dC ([C,H,W] each, kept for backward) and
+ *               igs_l1_ssim_partials(C,H,W) pairs {sum of the SSIM map, sum of |img1 - img2|}, one per
+ *               CTA; the caller adds them up: ssim = sum0 / (C*H*W), Ll1 = sum1 / (C*H*W).
+ *     backward: grad_img1 [C,H,W] = *grad_out * d loss / d img1 (grad_out: device scalar). */
+size_t igs_l1_ssim_partials(int32_t C, int32_t H, int32_t W);
+int igs_l1_ssim_forward(const float* img1, const float* img2, int32_t C, int32_t H, int32_t W, float* dA,
+                        float* dB, float* dC, float* partial, igs_stream_t stream);
+int igs_l1_ssim_backward(const float* img1, const float* img2, const float* dA, const float* dB,
+                         const float* dC, int32_t C, int32_t H, int32_t W, float lambda_dssim,
+                         const float* grad_out, float* grad_img1, igs_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,194 @@
+// the photometric loss on the rasterizer's colour output,
+//     loss = l1_loss(image, gt) + lambda_dssim * (1 - ssim(image, gt))
+// (reference train_face.py:421-422, utils/loss_utils.py:28-73), as two kernels that produce
+// dL/dimage -- the rasterizer backward's dL_dcolor input -- directly in CHW layout:
+//
+//   forward : per channel, separable 11-tap Gaussian window (sigma 1.5, zero padding 5) of
+//             {x, y, x^2, y^2, xy} through shared memory -> SSIM map -> per-CTA partial sums of
+//             the SSIM map and of |x - y|, plus three per-pixel derivative maps
+//                 A = df/dmu1 - 2 mu1 df/ds1 - mu2 df/ds12,  B = df/ds1,  C = df/ds12
+//   backward: dL/dx = g * ( sign(x - y)/N - lambda/N * (conv(A) + 2 x conv(B) + y conv(C)) )
+//             (the window is symmetric, so the adjoint of the convolution is the convolution).
+//
+// The reference runs 5 depthwise conv2d + ~15 element-wise kernels forward and their autograd
+// backward (another 5 transposed convolutions) and materialises ~12 full-frame temporaries.
+// HBM bound: forward reads 2 and writes 3 floats per pixel-channel, backward reads 5, writes 1.
+#include "igs_common.cuh"
+#include "igs_kernels.cuh"
+
+namespace igs {
+
+constexpr int LT = 16;            // output tile edge
+constexpr int LH = 5;             // window radius (window_size 11)
+constexpr int LR = LT + 2 * LH;   // 26 rows / columns with halo
+constexpr float SSIM_C1 = 0.01f * 0.01f, SSIM_C2 = 0.03f * 0.03f;
+
+struct Win { float w[11]; };
+
+// gaussian(11, 1.5) of utils/loss_utils.py:42-44, in fp32 like torch.Tensor([...]) / sum
+static Win make_window() {
+  Win k;
+  float s = 0.f;
+  for (int i = 0; i < 11; i++) { k.w[i] = (float)exp(-(double)((i - 5) * (i - 5)) / (2.0 * 1.5 * 1.5)); s += k.w[i]; }
+  for (int i = 0; i < 11; i++) k.w[i] = k.w[i] / s;
+  return k;
+}
+
+__global__ void __launch_bounds__(LT * LT) l1_ssim_forward_kernel(
+    const float* __restrict__ img1, const float* __restrict__ img2, int H, int W, Win win,
+    float* __restrict__ dA, float* __restrict__ dB, float* __restrict__ dC, float* __restrict__ partial) {
+  __shared__ float s_x[LR][LR + 1], s_y[LR][LR + 1];
+  __shared__ float s_h[5][LR][LT + 1];
+  __shared__ float s_red[2][LT * LT / 32];
+  const int c = blockIdx.z, tx = threadIdx.x % LT, ty = threadIdx.x / LT;
+  const int x0 = blockIdx.x * LT, y0 = blockIdx.y * LT;
+  const size_t plane = (size_t)c * H * W;
+  for (int i = threadIdx.x; i < LR * LR; i += LT * LT) {
+    const int ry = i / LR, rx = i % LR, gx = x0 - LH + rx, gy = y0 - LH + ry;
+    const bool in = gx >= 0 && gx < W && gy >= 0 && gy < H;
+    s_x[ry][rx] = in ? __ldg(img1 + plane + (size_t)gy * W + gx) : 0.f;
+    s_y[ry][rx] = in ? __ldg(img2 + plane + (size_t)gy * W + gx) : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < LR * LT; i += LT * LT) { // horizontal pass, 26 rows x 16 columns
+    const int ry = i / LT, rx = i % LT;
+    float sx = 0.f, sy = 0.f, sxx = 0.f, syy = 0.f, sxy = 0.f;
+#pragma unroll
+    for (int k = 0; k < 11; k++) {
+      const float w = win.w[k], a = s_x[ry][rx + k], b = s_y[ry][rx + k];
+      sx = fmaf(w, a, sx); sy = fmaf(w, b, sy);
+      sxx = fmaf(w, a * a, sxx); syy = fmaf(w, b * b, syy); sxy = fmaf(w, a * b, sxy);
+    }
+    s_h[0][ry][rx] = sx; s_h[1][ry][rx] = sy; s_h[2][ry][rx] = sxx; s_h[3][ry][rx] = syy; s_h[4][ry][rx] = sxy;
+  }
+  __syncthreads();
+  float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+  for (int k = 0; k < 11; k++) { // vertical pass
+    const float w = win.w[k];
+    mu1 = fmaf(w, s_h[0][ty + k][tx], mu1); mu2 = fmaf(w, s_h[1][ty + k][tx], mu2);
+    e11 = fmaf(w, s_h[2][ty + k][tx], e11); e22 = fmaf(w, s_h[3][ty + k][tx], e22);
+    e12 = fmaf(w, s_h[4][ty + k][tx], e12);
+  }
+  const int x = x0 + tx, y = y0 + ty;
+  const bool inside = x < W && y < H;
+  float ssim_v = 0.f, l1_v = 0.f;
+  if (inside) {
+    // utils/loss_utils.py:58-70
+    const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
+    const float s1 = e11 - mu1_sq, s2 = e22 - mu2_sq, s12 = e12 - mu12;
+    const float a1 = 2.f * mu12 + SSIM_C1, a2 = 2.f * s12 + SSIM_C2;
+    const float b1 = mu1_sq + mu2_sq + SSIM_C1, b2 = s1 + s2 + SSIM_C2;
+    const float inv = 1.f / (b1 * b2);
+    const float f = a1 * a2 * inv;
+    ssim_v = f;
+    const float df_dmu1 = 2.f * mu2 * a2 * inv - f * 2.f * mu1 / b1;
+    const float df_ds1 = -f / b2;
+    const float df_ds12 = 2.f * a1 * inv;
+    const size_t pix = plane + (size_t)y * W + x;
+    dA[pix] = df_dmu1 - 2.f * mu1 * df_ds1 - mu2 * df_ds12;
+    dB[pix] = df_ds1;
+    dC[pix] = df_ds12;
+    l1_v = fabsf(s_x[ty + LH][tx + LH] - s_y[ty + LH][tx + LH]);
+  }
+  // per-CTA partial sums (summed by the host wrapper: deterministic, no float atomics)
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    ssim_v += __shfl_xor_sync(0xffffffffu, ssim_v, o);
+    l1_v += __shfl_xor_sync(0xffffffffu, l1_v, o);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) { s_red[0][warp] = ssim_v; s_red[1][warp] = l1_v; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f, b = 0.f;
+    for (int w = 0; w < LT * LT / 32; w++) { a += s_red[0][w]; b += s_red[1][w]; }
+    const size_t cta = ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    partial[2 * cta] = a;
+    partial[2 * cta + 1] = b;
+  }
+}
+
+__global__ void __launch_bounds__(LT * LT) l1_ssim_backward_kernel(
+    const float* __restrict__ img1, const float* __restrict__ img2, const float* __restrict__ dA,
+    const float* __restrict__ dB, const float* __restrict__ dC, int H, int W, Win win, float lambda_dssim,
+    const float* __restrict__ grad_out, float inv_n, float* __restrict__ grad_img1) {
+  __shared__ float s_m[3][LR][LR + 1];
+  __shared__ float s_h[3][LR][LT + 1];
+  const int c = blockIdx.z, tx = threadIdx.x % LT, ty = threadIdx.x / LT;
+  const int x0 = blockIdx.x * LT, y0 = blockIdx.y * LT;
+  const size_t plane = (size_t)c * H * W;
+  for (int i = threadIdx.x; i < LR * LR; i += LT * LT) {
+    const int ry = i / LR, rx = i % LR, gx = x0 - LH + rx, gy = y0 - LH + ry;
+    const bool in = gx >= 0 && gx < W && gy >= 0 && gy < H;
+    const size_t p = plane + (size_t)gy * W + gx;
+    s_m[0][ry][rx] = in ? __ldg(dA + p) : 0.f;
+    s_m[1][ry][rx] = in ? __ldg(dB + p) : 0.f;
+    s_m[2][ry][rx] = in ? __ldg(dC + p) : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < LR * LT; i += LT * LT) {
+    const int ry = i / LT, rx = i % LT;
+    float a = 0.f, b = 0.f, d = 0.f;
+#pragma unroll
+    for (int k = 0; k < 11; k++) {
+      const float w = win.w[k];
+      a = fmaf(w, s_m[0][ry][rx + k], a); b = fmaf(w, s_m[1][ry][rx + k], b); d = fmaf(w, s_m[2][ry][rx + k], d);
+    }
+    s_h[0][ry][rx] = a; s_h[1][ry][rx] = b; s_h[2][ry][rx] = d;
+  }
+  __syncthreads();
+  const int x = x0 + tx, y = y0 + ty;
+  if (x >= W || y >= H) return;
+  float ca = 0.f, cb = 0.f, cc = 0.f;
+#pragma unroll
+  for (int k = 0; k < 11; k++) {
+    const float w = win.w[k];
+    ca = fmaf(w, s_h[0][ty + k][tx], ca); cb = fmaf(w, s_h[1][ty + k][tx], cb); cc = fmaf(w, s_h[2][ty + k][tx], cc);
+  }
+  const size_t pix = plane + (size_t)y * W + x;
+  const float xv = __ldg(img1 + pix), yv = __ldg(img2 + pix);
+  const float d = xv - yv;
+  const float sgn = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f); // torch.abs backward: sign(0) = 0
+  const float dssim = ca + 2.f * xv * cb + yv * cc;          // sum_q d ssim_q / d x_p
+  grad_img1[pix] = __ldg(grad_out) * inv_n * (sgn - lambda_dssim * dssim);
+}
+
+} // namespace igs
+
+using namespace igs;
+
+extern "C" {
+
+size_t igs_l1_ssim_partials(int32_t C, int32_t H, int32_t W) {
+  return (size_t)(C > 0 ? C : 0) * ((H + LT - 1) / LT) * ((W + LT - 1) / LT);
+}
+
+int igs_l1_ssim_forward(const float* img1, const float* img2, int32_t C, int32_t H, int32_t W, float* dA,
+                        float* dB, float* dC, float* partial, igs_stream_t stream) {
+  if (C <= 0 || H <= 0 || W <= 0 || !img1 || !img2 || !dA || !dB || !dC || !partial) {
+    set_error("l1_ssim forward: bad arguments"); return IGS_ERR_INVALID;
+  }
+  static const Win win = make_window();
+  const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C);
+  l1_ssim_forward_kernel<<<grid, LT * LT, 0, (cudaStream_t)stream>>>(img1, img2, H, W, win, dA, dB, dC, partial);
+  count_launch();
+  return stage_check(false, (cudaStream_t)stream, "l1_ssim forward");
+}
+
+int igs_l1_ssim_backward(const float* img1, const float* img2, const float* dA, const float* dB, const float* dC,
+                         int32_t C, int32_t H, int32_t W, float lambda_dssim, const float* grad_out,
+                         float* grad_img1, igs_stream_t stream) {
+  if (C <= 0 || H <= 0 || W <= 0 || !img1 || !img2 || !dA || !dB || !dC || !grad_out || !grad_img1) {
+    set_error("l1_ssim backward: bad arguments"); return IGS_ERR_INVALID;
+  }
+  static const Win win = make_window();
+  const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C);
+  const float inv_n = 1.0f / ((float)C * (float)H * (float)W);
+  l1_ssim_backward_kernel<<<grid, LT * LT, 0, (cudaStream_t)stream>>>(img1, img2, dA, dB, dC, H, W, win, lambda_dssim,
+                                                                      grad_out, inv_n, grad_img1);
+  count_launch();
+  return stage_check(false, (cudaStream_t)stream, "l1_ssim backward");
+}
+
+} // extern "C"

@@ -95,3 +95,49 @@ def densify_stats(radii, grad_means2D, max_radii2D, xyz_gradient_accum, denom):
     acc.reshape(-1)[vis] += nrm
     den.reshape(-1)[vis] += F32(1)
     return mr, acc, den
+
+
+def _ssim_window(window_size=11, sigma=1.5):
+    """utils/loss_utils.py:42-50: fp32 1-D Gaussian, normalised, outer product."""
+    g = np.array([np.exp(-(x - window_size // 2) ** 2 / float(2 * sigma ** 2)) for x in range(window_size)], F32)
+    g = (g / g.sum(dtype=F32)).astype(F32)
+    return np.outer(g, g).astype(F32)
+
+
+def _conv_same(img, win):
+    """F.conv2d(img, window, padding=window_size//2, groups=channel) for [C,H,W], float64 accumulation."""
+    C, H, W = img.shape
+    k = win.shape[0]
+    pad = k // 2
+    p = np.zeros((C, H + 2 * pad, W + 2 * pad), np.float64)
+    p[:, pad:pad + H, pad:pad + W] = img
+    out = np.zeros((C, H, W), np.float64)
+    for dy in range(k):
+        for dx in range(k):
+            out += float(win[dy, dx]) * p[:, dy:dy + H, dx:dx + W]
+    return out
+
+
+def l1_ssim_loss(image, gt, lambda_dssim=0.2):
+    """train_face.py:421-422 with utils/loss_utils.py:28-29,52-73.  Returns (loss, Ll1, ssim, dloss/dimage)
+    (float64 arithmetic; the gradient is the analytic adjoint of the same expression)."""
+    x, y = np.asarray(image, np.float64), np.asarray(gt, np.float64)
+    win = _ssim_window()
+    mu1, mu2 = _conv_same(x, win), _conv_same(y, win)
+    s1 = _conv_same(x * x, win) - mu1 * mu1
+    s2 = _conv_same(y * y, win) - mu2 * mu2
+    s12 = _conv_same(x * y, win) - mu1 * mu2
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    a1, a2 = 2 * mu1 * mu2 + C1, 2 * s12 + C2
+    b1, b2 = mu1 * mu1 + mu2 * mu2 + C1, s1 + s2 + C2
+    f = a1 * a2 / (b1 * b2)
+    n = x.size
+    ssim, l1 = f.mean(), np.abs(x - y).mean()
+    loss = l1 + lambda_dssim * (1.0 - ssim)
+    df_dmu1 = 2 * mu2 * a2 / (b1 * b2) - f * 2 * mu1 / b1
+    df_ds1 = -f / b2
+    df_ds12 = 2 * a1 / (b1 * b2)
+    A = df_dmu1 - 2 * mu1 * df_ds1 - mu2 * df_ds12
+    dssim = _conv_same(A, win) + 2 * x * _conv_same(df_ds1, win) + y * _conv_same(df_ds12, win)
+    grad = (np.sign(x - y) - lambda_dssim * dssim) / n
+    return float(loss), float(l1), float(ssim), grad.astype(F32)

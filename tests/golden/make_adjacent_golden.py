@@ -77,7 +77,23 @@ def densify_case(P, seed):
     return before
 
 
+def loss_case(H, W, seed, lam=0.2):
+    """Imports the reference's OWN utils/loss_utils.py (plain torch) from /root/reference."""
+    import sys
+    sys.path.insert(0, "/root/reference")
+    from utils.loss_utils import l1_loss, ssim  # utils/loss_utils.py:28-29, 52-73
+    g = torch.Generator().manual_seed(seed)
+    gt = torch.rand((3, H, W), generator=g)
+    image = (gt + 0.15 * torch.randn((3, H, W), generator=g)).clamp(0, 1).requires_grad_(True)
+    Ll1 = l1_loss(image, gt)                                      # train_face.py:421
+    loss = Ll1 + lam * (1.0 - ssim(image, gt))                    # train_face.py:422
+    (3.0 * loss).backward()
+    return dict(image=image.detach().numpy(), gt=gt.numpy(), lam=np.float32(lam), loss=loss.detach().numpy(),
+                l1=Ll1.detach().numpy(), ssim=ssim(image.detach(), gt).numpy(), grad_x3=image.grad.numpy())
+
+
 if __name__ == "__main__":
+    np.savez_compressed(os.path.join(HERE, "adjacent_loss.npz"), **loss_case(45, 61, 5))
     np.savez_compressed(os.path.join(HERE, "adjacent_compose_plain.npz"), **compose_case(37, 53, 1, False))
     np.savez_compressed(os.path.join(HERE, "adjacent_compose_dilate.npz"), **compose_case(48, 40, 2, True))
     np.savez_compressed(os.path.join(HERE, "adjacent_activate.npz"), **activate_case(257, 3))

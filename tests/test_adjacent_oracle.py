@@ -60,3 +60,10 @@ def test_densify_stats():
     assert np.array_equal(den, g["out_denom"])
     inv = g["radii"] <= 0
     assert np.array_equal(acc[inv], g["xyz_gradient_accum"][inv]) and np.array_equal(mr[inv], g["max_radii2D"][inv])
+
+
+def test_l1_ssim_loss_matches_the_references_loss_utils():
+    g = _load("adjacent_loss.npz")  # made by importing /root/reference/utils/loss_utils.py
+    loss, l1, ss, grad = A.l1_ssim_loss(g["image"], g["gt"], float(g["lam"]))
+    assert abs(loss - float(g["loss"])) <= 1e-6 and abs(l1 - float(g["l1"])) <= 1e-6 and abs(ss - float(g["ssim"])) <= 1e-6
+    assert np.abs(3 * grad - g["grad_x3"]).max() <= 1e-5 * np.abs(g["grad_x3"]).max()

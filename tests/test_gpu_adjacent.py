@@ -117,3 +117,110 @@ def test_adjacent_entry_points_reject_cpu_tensors():
         SY.compose_frame(torch.zeros(3, 4, 4), torch.zeros(1, 4, 4), torch.zeros(3, 4, 4), torch.zeros(1, 4, 4))
     with pytest.raises(RuntimeError, match="CUDA-only"):
         TO.activate_gaussians(torch.zeros(2, 3), torch.zeros(2, 3), torch.zeros(2, 4), torch.zeros(2, 1))
+
+
+def test_ply_asset_renders_like_the_tensors_it_was_written_from(tmp_path):
+    """f4: save_ply-format file -> read -> fused activations -> GaussianRasterizer == direct call."""
+    import torch
+    from diff_gauss import GaussianRasterizer
+    from instag_b200 import assets as AS, synthetic as S, training_ops as TO
+    rng = np.random.default_rng(3)
+    P, deg = 3000, 2
+    K = (deg + 1) ** 2
+    raw = dict(xyz=rng.uniform(-0.1, 0.1, (P, 3)).astype(np.float32),
+               features_dc=rng.normal(0, 0.5, (P, 1, 3)).astype(np.float32),
+               features_rest=rng.normal(0, 0.1, (P, K - 1, 3)).astype(np.float32),
+               opacity=rng.normal(0, 2, (P, 1)).astype(np.float32),
+               scaling=rng.normal(-4.5, 0.4, (P, 3)).astype(np.float32),
+               rotation=rng.normal(0, 1, (P, 4)).astype(np.float32))
+    path = os.path.join(tmp_path, "point_cloud.ply")
+    AS.write_gaussian_ply(path, **raw)
+    g = AS.read_gaussian_ply(path, max_sh_degree=deg)
+    ins = AS.rasterizer_inputs(g)
+    cam = U.to_torch(dict(S.make_camera(96, 80), bg=np.zeros(3, np.float32)))
+    cam["sh_degree"] = deg
+    rs = U.settings_from(cam)
+    m2 = torch.zeros_like(ins["means3D"])
+    a = GaussianRasterizer(rs)(means3D=ins["means3D"], means2D=m2, shs=ins["shs"], opacities=ins["opacities"],
+                               scales=ins["scales"], rotations=ins["rotations"])
+    t = lambda k: _t(raw[k])
+    m, s, r, o = TO.activate_gaussians(t("xyz"), t("scaling"), t("rotation"), t("opacity"))
+    b = GaussianRasterizer(rs)(means3D=m, means2D=m2, shs=torch.cat([t("features_dc"), t("features_rest")], 1).contiguous(),
+                               opacities=o, scales=s, rotations=r)
+    assert int((a[4] > 0).sum()) > 100
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+
+
+def test_l1_ssim_loss_matches_golden_and_oracle():
+    """f3: loss within 1e-6, gradient within 1e-4 of its max (fp32 separable window vs torch conv2d)."""
+    import torch
+    from instag_b200 import losses as LS
+    g = dict(np.load(os.path.join(G, "adjacent_loss.npz")))
+    img = _t(g["image"]).requires_grad_(True)
+    loss, l1, ss = LS.l1_ssim_loss(img, _t(g["gt"]), float(g["lam"]), return_terms=True)
+    assert abs(float(loss.detach()) - float(g["loss"])) <= 1e-6 and abs(float(l1) - float(g["l1"])) <= 1e-6
+    assert abs(float(ss) - float(g["ssim"])) <= 1e-6
+    (3.0 * loss).backward()
+    assert np.abs(img.grad.cpu().numpy() - g["grad_x3"]).max() <= 1e-4 * np.abs(g["grad_x3"]).max()
+    # ragged size, identical images (ssim = 1, |x - y| = 0 -> sign 0), one channel
+    rng = np.random.default_rng(2)
+    for shape in ((3, 75, 50), (1, 16, 16), (3, 512, 512)):
+        x = rng.random(shape, dtype=np.float32)
+        y = np.clip(x + 0.1 * rng.standard_normal(shape).astype(np.float32), 0, 1)
+        wl, w1, ws, wg = A.l1_ssim_loss(x, y, 0.2)
+        tx = _t(x).requires_grad_(True)
+        gl, g1, gs = LS.l1_ssim_loss(tx, _t(y), 0.2, return_terms=True)
+        gl.backward()
+        assert abs(float(gl.detach()) - wl) <= 2e-6 and abs(float(gs) - ws) <= 2e-6, shape
+        assert np.abs(tx.grad.cpu().numpy() - wg).max() <= 1e-4 * np.abs(wg).max(), shape
+    same = _t(rng.random((3, 40, 40), dtype=np.float32)).requires_grad_(True)
+    l0 = LS.l1_ssim_loss(same, same.detach().clone(), 0.2)
+    l0.backward()
+    assert abs(float(l0.detach())) <= 1e-6 and float(same.grad.abs().max()) <= 1e-6
+
+
+def test_l1_ssim_gradient_feeds_the_rasterizer_backward():
+    """End of the chain f3 -> a12: loss on the rendered colour -> dL_dcolor -> per-Gaussian gradients,
+    against the same chain with the reference's torch loss."""
+    import sys
+    import torch
+    from diff_gauss import GaussianRasterizer
+    from instag_b200 import losses as LS
+    sc = U.make_scene(P=2500, W=80, H=64, sh_degree=None, ED=1, scale_mult=2.0, seed=31)
+    t = U.to_torch(sc)
+    gt = torch.rand((3, 64, 80), device="cuda", generator=torch.Generator("cuda").manual_seed(1))
+
+    def run(fused):
+        col = t["colors_precomp"].clone().requires_grad_(True)
+        op = t["opacities"].clone().requires_grad_(True)
+        out = GaussianRasterizer(U.settings_from(t))(
+            means3D=t["means3D"], means2D=torch.zeros_like(t["means3D"]), colors_precomp=col, opacities=op,
+            scales=t["scales"], rotations=t["rotations"], extra_attrs=t["extra_attrs"])
+        if fused:
+            loss = LS.l1_ssim_loss(out[0], gt, 0.2)
+        else:
+            loss = (out[0] - gt).abs().mean() + 0.2 * (1.0 - _torch_ssim(out[0], gt))
+        loss.backward()
+        return float(loss), col.grad, op.grad
+
+    a, b = run(True), run(False)
+    assert abs(a[0] - b[0]) <= 2e-6
+    for x, y in zip(a[1:], b[1:]):
+        assert float((x - y).abs().max()) <= 2e-4 * float(y.abs().max())
+
+
+def _torch_ssim(img1, img2):
+    """utils/loss_utils.py:42-73 restated with torch ops (the reference file itself is not on the GPU box)."""
+    import torch
+    import torch.nn.functional as F
+    g = torch.tensor([np.exp(-(x - 5) ** 2 / float(2 * 1.5 ** 2)) for x in range(11)], dtype=torch.float32)
+    g = (g / g.sum()).unsqueeze(1)
+    C_ = img1.size(-3)
+    w = g.mm(g.t()).float().unsqueeze(0).unsqueeze(0).expand(C_, 1, 11, 11).contiguous().to(img1.device)
+    mu1, mu2 = F.conv2d(img1, w, padding=5, groups=C_), F.conv2d(img2, w, padding=5, groups=C_)
+    s1 = F.conv2d(img1 * img1, w, padding=5, groups=C_) - mu1.pow(2)
+    s2 = F.conv2d(img2 * img2, w, padding=5, groups=C_) - mu2.pow(2)
+    s12 = F.conv2d(img1 * img2, w, padding=5, groups=C_) - mu1 * mu2
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    return (((2 * mu1 * mu2 + C1) * (2 * s12 + C2)) / ((mu1.pow(2) + mu2.pow(2) + C1) * (s1 + s2 + C2))).mean()

@@ -318,19 +318,43 @@ def main():
     arm = Arm(a.impl, sc, grads, device)
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=device)
 
+    # the exchange step of a view-sharded batch: the packed gradient block lives in NVLink multicast
+    # memory and is summed by ONE hand-written kernel (igs_allreduce_nvls); NCCL if NVLS is unavailable
+    block, collective = None, "none"
+    if eff_world > 1 and backward:
+        collective = "NCCL all-reduce"
+        if not os.environ.get("IGS_BENCH_NCCL"):
+            try:
+                M_ = sc["shs"].shape[1] if sc.get("shs") is not None else 0
+                block = SHD.NvlsGradientBlock(P, M_, 1, device)
+                block.__enter__()  # every backward of this process now writes its gradients into the block
+                collective = "igs_allreduce_nvls (multimem.ld_reduce/st over NVLink multicast memory)"
+            except Exception as ex:  # no symmetric memory / multicast on this system
+                collective = f"NCCL all-reduce (NVLS unavailable: {str(ex)[:80]})"
+
+    a.collective = collective
+
     def step():
         if not backward:
             return arm.step_fwd_only()
         res = arm.step_raw()
         if eff_world > 1:
-            SHD.allreduce_view_gradients(res)  # ONE all-reduce: the ten gradients share one allocation
+            # ONE collective over the contiguous prefix of the packed block that holds the parameter gradients
+            if block is not None:
+                block.all_reduce()
+            else:
+                SHD.allreduce_view_gradients(res, only_parameters=True)
         return res
 
     def step_e2e():
         out = arm.step_e2e()
         if eff_world > 1:
-            for v in out[0].values():
-                dist.all_reduce(v.grad)
+            grads_ = [v.grad for v in out[0].values()]
+            if block is not None and block.holds(grads_):
+                block.all_reduce()
+            else:
+                for g_ in grads_:
+                    dist.all_reduce(g_)
         return out
 
     if a.impl == "igs":
@@ -398,8 +422,9 @@ def finish(a, cfg, sc, grads, arm, world, rank, ms, per, wall, value, e2e, clock
                                f"{'precomputed colours' if S_ == 0 else 'SH deg %d M=%d' % (cfg['sh_degree'], cfg['M'])}"
                                f", ED=1, {'forward+backward' if backward else 'forward only'}, one camera per rank",
                    "num_rendered": N, "frames_per_step": world,
-                   "parallelism": "single GPU" if world == 1 else f"view-sharded dp{world} + NCCL all-reduce of packed "
-                                                                  f"per-Gaussian grads",
+                   "parallelism": "single GPU" if world == 1 else f"view-sharded dp{world} + ONE collective over the packed "
+                                                                  f"per-Gaussian parameter gradients (means3D, colour/SH, "
+                                                                  f"opacity, scales, rotations, extra): {getattr(a, 'collective', 'none')}",
                    "l2": "flushed between steps (256 MiB memset outside the per-step event pairs)",
                    "timing": "sum of per-step CUDA-event pairs / K, max over ranks"},
         "e2e": e2e, "clocks": clocks, "wall_s_timed_region": wall,

@@ -239,6 +239,20 @@ int igs_activate_backward(int32_t P, const float* scaling, const float* d_scale,
 int igs_densify_stats(int32_t P, const int32_t* radii, const float* grad_means2D, float* max_radii2D,
                       float* xyz_gradient_accum, float* denom, igs_stream_t stream);
 
+/* ---- the exchange step of a view-sharded batch ----------------------------
+ * igs_allreduce_nvls sums n_floats fp32 values (a multiple of 4) in place over the `world` GPUs of
+ * one NVSwitch box, in ONE kernel over NVLink multicast memory (multimem.ld_reduce / multimem.st,
+ * flag barriers through the peers' signal pads).  It replaces the ncclAllReduce of the packed
+ * per-Gaussian gradient block (the reference has no multi-GPU path: north star).
+ *   multicast_ptr       : the MULTICAST address of the buffer (same offset on every rank)
+ *   signal_pad_ptrs_dev : device array of `world` pointers to the ranks' signal pads (zeroed;
+ *                         signal_pad_bytes each, of which the bytes from 1024 on are used: one
+ *                         4-byte flag per (CTA, peer), so the pad size bounds the CTA count)
+ * as handed out by torch.distributed._symmetric_memory (multicast_ptr, signal_pad_ptrs_dev);
+ * every rank must call it with the same n_floats on its own stream (instag_b200/sharding.py). */
+int igs_allreduce_nvls(void* multicast_ptr, void* signal_pad_ptrs_dev, int32_t signal_pad_bytes,
+                       int32_t rank, int32_t world, int64_t n_floats, igs_stream_t stream);
+
 /* f3  igs_l1_ssim_* replace the photometric loss on the rasterizer's colour output,
  *         Ll1 = l1_loss(image, gt);  loss = Ll1 + lambda_dssim * (1.0 - ssim(image, gt))
  *     (/root/reference/train_face.py:421-422, utils/loss_utils.py:28-73: 11x11 Gaussian window,

@@ -77,6 +77,7 @@ SYMBOLS = {
     "igs_activate_forward": (C.c_int, [C.c_int32] + [_p] * 12),
     "igs_activate_backward": (C.c_int, [C.c_int32] + [_p] * 14),
     "igs_densify_stats": (C.c_int, [C.c_int32] + [_p] * 6),
+    "igs_allreduce_nvls": (C.c_int, [_p, _p, C.c_int32, C.c_int32, C.c_int32, C.c_int64, _p]),
     "igs_l1_ssim_partials": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
     "igs_l1_ssim_forward": (C.c_int, [_p, _p, C.c_int32, C.c_int32, C.c_int32, _p, _p, _p, _p, _p]),
     "igs_l1_ssim_backward": (C.c_int, [_p, _p, _p, _p, _p, C.c_int32, C.c_int32, C.c_int32, C.c_float, _p, _p, _p]),

@@ -189,6 +189,35 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
     return num_rendered, color, depth, norm, alpha, radii, extra, geom, binb, img
 
 
+def gradient_layout(P, M, ED):
+    """Layout of the ONE allocation behind the ten gradient tensors `_backward_native` returns, in
+    its return order (means2D, colours, opacity, means3D, cov3D, norm3D, sh, scales, rotations,
+    extra): (starts, widths, total floats, floats of the parameter prefix).  Every block starts
+    16-byte aligned, as the C ABI requires.  The gradients of trainable parameters come first and
+    are contiguous (means3D, colours, opacity, SH, scales, rotations, extra), so that a view-sharded
+    batch can all-reduce just that prefix (sharding.py); means2D (per-view densification statistics
+    only) and the cov3D / norm3D intermediates follow."""
+    widths = [3, 3, 1, 3, 6, 3, 3 * M, 3, 4, ED]
+    starts, o, param_end = [0] * len(widths), 0, 0
+    for i in (3, 1, 2, 6, 7, 8, 9, 0, 4, 5):
+        if i == 0:
+            param_end = o
+        starts[i] = o
+        o += (P * widths[i] + 3) // 4 * 4
+    return starts, widths, o, param_end
+
+
+# optional allocator of the packed gradient block: fn(n_floats, device) -> flat float32 tensor.
+# sharding.NvlsGradientBlock installs one so that the block lives in NVLink multicast memory.
+_grad_alloc = None
+
+
+def set_gradient_allocator(fn):
+    global _grad_alloc
+    prev, _grad_alloc = _grad_alloc, fn
+    return prev
+
+
 def _backward_native(bg, means3D, radii, colors_precomp, scales, rotations, extra_attrs, scale_modifier,
                      cov3Ds_precomp, norm3Ds_precomp, viewmatrix, projmatrix, tanfovx, tanfovy,
                      dL_dcolor, dL_ddepth, dL_dnorm, dL_dalpha, dL_dextra, sh, sh_degree, campos, geom,
@@ -204,13 +233,8 @@ def _backward_native(bg, means3D, radii, colors_precomp, scales, rotations, extr
     stream = torch.cuda.current_stream(dev).cuda_stream
     sc = _get_scratch(dev, stream)
     # one allocation for all per-Gaussian gradients, contiguous sub-blocks
-    widths = [3, 3, 1, 3, 6, 3, 3 * M, 3, 4, ED]
-    # (every block starts 16-byte aligned, as the C ABI requires)
-    starts, o = [], 0
-    for w in widths:
-        starts.append(o)
-        o += (P * w + 3) // 4 * 4
-    flat = torch.empty((o,), dtype=torch.float32, device=dev)
+    starts, widths, total, _ = gradient_layout(P, M, ED)
+    flat = _grad_alloc(total, dev) if _grad_alloc is not None else torch.empty((total,), dtype=torch.float32, device=dev)
     outs = [flat[st:st + P * w].view(P, w) for st, w in zip(starts, widths)]
     (g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_norm3D, g_sh, g_scales, g_rot, g_extra) = outs
     g_sh = g_sh.view(P, M, 3)

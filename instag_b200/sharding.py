@@ -29,22 +29,109 @@ def packed_base(grad):
     return grad._base if grad._base is not None else grad
 
 
-def allreduce_view_gradients(grads, group=None):
+# positions of the trainable-parameter gradients in the tuple `_backward_native` returns
+# (means2D, colours, opacity, means3D, cov3D, norm3D, sh, scales, rotations, extra)
+PARAMETER_GRADS = (1, 2, 3, 6, 7, 8, 9)
+
+
+def allreduce_view_gradients(grads, group=None, only_parameters=False):
     """Sum the per-Gaussian gradients of this rank's views with everybody else's, in place.
 
     grads: the tuple `_backward_native` returned (or any tensors that are views of one block).
-    One collective for all of them when they share a base, else one per tensor."""
+    One collective for all of them when they share a base, else one per tensor.
+    only_parameters: reduce just the gradients an optimizer consumes (PARAMETER_GRADS: 15 + 3M of the
+    27 + 3M packed floats per Gaussian).  The means2D gradient only feeds the per-view densification
+    statistics (reduce_densification_stats, which needs it un-summed), and the cov3D / norm3D
+    gradients belong to inputs InsTaG never passes (gaussian_renderer/__init__.py:237 cov3D_precomp =
+    None); `_backward_native` lays the parameter gradients out as one contiguous prefix for this."""
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
         return grads
+    sel = [g for i, g in enumerate(grads) if (not only_parameters or i in PARAMETER_GRADS)]
+    sel = [g for g in sel if g is not None and g.numel() != 0]
     bases = {}
-    for g in grads:
-        if g is None or g.numel() == 0:
-            continue
+    for g in sel:
         b = packed_base(g)
-        bases[b.data_ptr()] = b
-    for b in bases.values():
-        dist.all_reduce(b, op=dist.ReduceOp.SUM, group=group)
+        bases.setdefault(b.data_ptr(), (b, []))[1].append(g)
+    for b, members in bases.values():
+        if b.dim() == 1 and b.is_contiguous():
+            # the smallest range of the block that covers the selected tensors (whole block if all are)
+            lo = min(g.storage_offset() for g in members) - b.storage_offset()
+            hi = max(g.storage_offset() + g.numel() for g in members) - b.storage_offset()
+            dist.all_reduce(b[lo:hi], op=dist.ReduceOp.SUM, group=group)
+        else:
+            dist.all_reduce(b, op=dist.ReduceOp.SUM, group=group)
     return grads
+
+
+class NvlsGradientBlock:
+    """Home of the packed gradient block in NVLink multicast (symmetric) memory, and its all-reduce
+    as ONE hand-written kernel (`igs_allreduce_nvls`: multimem.ld_reduce + multimem.st with flag
+    barriers, csrc/igs_collective.cu) instead of ncclAllReduce.
+
+        block = NvlsGradientBlock(P, M, ED, device)        # collective: every rank, once
+        with block:                                         # backward writes its gradients into it
+            loss.backward()   (or _backward_native(...))
+        block.all_reduce()                                  # parameter-gradient prefix, in place
+
+    Two buffers alternate, so the gradients of one step stay valid while the next step runs.
+    Raises RuntimeError when symmetric memory / multicast is unavailable (callers fall back to
+    `allreduce_view_gradients`, i.e. NCCL)."""
+
+    def __init__(self, P, M, ED, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        from . import rasterizer as R
+        from . import _native as N
+        self.N = N
+        self.R = R
+        self.group = dist.group.WORLD if group is None else group
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        _, _, total, param_end = R.gradient_layout(P, M, ED)
+        self.total, self.param_end = total, param_end
+        self.device = torch.device(device)
+        self.bufs, self.hdls = [], []
+        for _ in range(2):
+            t = symm_mem.empty(total, dtype=torch.float32, device=self.device)
+            h = symm_mem.rendezvous(t, self.group.group_name)
+            if not getattr(h, "multicast_ptr", 0):
+                raise RuntimeError("NVLink multicast (NVLS) is not available for this group")
+            if h.signal_pad_size < 1024 + 4 * self.world:
+                raise RuntimeError("symmetric-memory signal pad too small")
+            self.bufs.append(t)
+            self.hdls.append(h)
+        self.cur = 0
+        self._prev = None
+
+    def _alloc(self, n_floats, device):
+        if n_floats != self.total or torch.device(device) != self.device:
+            raise RuntimeError("NvlsGradientBlock was sized for another (P, M, ED) or device")
+        self.cur ^= 1
+        return self.bufs[self.cur]
+
+    def __enter__(self):
+        self._prev = self.R.set_gradient_allocator(self._alloc)
+        return self
+
+    def __exit__(self, *exc):
+        self.R.set_gradient_allocator(self._prev)
+        return False
+
+    def holds(self, tensors):
+        """True if every given tensor lives inside the buffer the last backward wrote (e.g. the .grad
+        of the leaves after loss.backward()), i.e. one all_reduce() of the block covers them all."""
+        buf = self.bufs[self.cur]
+        lo, hi = buf.data_ptr(), buf.data_ptr() + 4 * (self.param_end)
+        return all(t is not None and lo <= t.data_ptr() and t.data_ptr() + 4 * t.numel() <= hi for t in tensors)
+
+    def all_reduce(self, only_parameters=True):
+        """Sum the block written by the last backward over the ranks, in place (current stream)."""
+        h = self.hdls[self.cur]
+        n = self.param_end if only_parameters else self.total
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        with torch.cuda.device(self.device):
+            self.N.check(self.N.lib().igs_allreduce_nvls(h.multicast_ptr + getattr(h, "offset", 0), h.signal_pad_ptrs_dev,
+                                                         int(h.signal_pad_size), self.rank, self.world, n, stream),
+                         "allreduce_nvls")
+        return self.bufs[self.cur]
 
 
 def reduce_densification_stats(grad_means2D, radii, group=None):

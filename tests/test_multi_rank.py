@@ -20,12 +20,13 @@ def _free_port():
 
 
 def _packed_grads(P, M, ED, seed):
-    """Same layout as rasterizer._backward_native: ten views of one flat block."""
+    """Same layout as rasterizer._backward_native: ten views of one flat block, the parameter
+    gradients (SH.PARAMETER_GRADS) first and contiguous."""
     widths = [3, 3, 1, 3, 6, 3, 3 * M, 3, 4, ED]
-    starts, o = [], 0
-    for w in widths:
-        starts.append(o)
-        o += (P * w + 3) // 4 * 4
+    starts, o = [0] * len(widths), 0
+    for i in (3, 1, 2, 6, 7, 8, 9, 0, 4, 5):
+        starts[i] = o
+        o += (P * widths[i] + 3) // 4 * 4
     g = torch.Generator().manual_seed(seed)
     flat = torch.randn(o, generator=g)
     return flat, [flat[s:s + P * w].view(P, w) for s, w in zip(starts, widths)]
@@ -54,6 +55,10 @@ def _worker(rank, world, port, n_views, n_frames, q):
             rmax = torch.maximum(rmax, radii)
         assert all(SH.packed_base(v).data_ptr() == flat.data_ptr() for v in views)
         SH.allreduce_view_gradients(views)
+        # only the parameter gradients: the others keep this rank's local sums
+        f2, v2 = _packed_grads(P, M, ED, seed=500 + rank)
+        keep = f2.clone()
+        SH.allreduce_view_gradients(v2, only_parameters=True)
         dist.all_reduce(stats_sum)
         dist.all_reduce(stats_cnt)
         dist.all_reduce(rmax, op=dist.ReduceOp.MAX)
@@ -66,7 +71,7 @@ def _worker(rank, world, port, n_views, n_frames, q):
         local = torch.stack([torch.full((2, 3), float(i)) for i in fr]) if fr else torch.zeros((0, 2, 3))
         full = SH.gather_frames(local, n_frames, rank, world)
         if rank == 0:
-            q.put(dict(flat=flat.numpy().copy(), ssum=stats_sum.numpy().copy(), scnt=stats_cnt.numpy().copy(),
+            q.put(dict(part=[t.numpy().copy() for t in v2], part_local=keep.numpy().copy(), flat=flat.numpy().copy(), ssum=stats_sum.numpy().copy(), scnt=stats_cnt.numpy().copy(),
                        rmax=rmax.numpy().copy(), full=full.numpy().copy(), hs=hs.numpy().copy(),
                        hc=hc.numpy().copy(), hr=hr.numpy().copy()))
     finally:
@@ -97,7 +102,14 @@ def test_world2_gradient_reduction_and_frame_gather():
     # single-process truth
     P, M, ED = 257, 4, 1
     flat = sum(_packed_grads(P, M, ED, seed=v)[0] for v in range(n_views))
-    np.testing.assert_allclose(out["flat"], flat.numpy(), rtol=1e-6, atol=1e-6)
+    used = 3 * P  # the block's trailing alignment padding (after norm3D, the last view) is not reduced
+    end = flat.numel() - ((3 * P + 3) // 4 * 4 - used)
+    np.testing.assert_allclose(out["flat"][:end], flat.numpy()[:end], rtol=1e-6, atol=1e-6)
+    # only_parameters: parameter gradients summed over the ranks, the rest untouched (rank 0's own)
+    per_rank = [_packed_grads(P, M, ED, seed=500 + r)[1] for r in range(world)]
+    for i in range(10):
+        want = sum(v[i] for v in per_rank) if i in SH.PARAMETER_GRADS else per_rank[0][i]
+        np.testing.assert_allclose(out["part"][i], want.numpy(), rtol=1e-6, atol=1e-6, err_msg=str(i))
     ssum = np.zeros((P, 1), np.float32)
     scnt = np.zeros((P, 1), np.float32)
     rmax = np.zeros(P, np.int32)

@@ -94,6 +94,11 @@ typedef struct IgsFwdArgs {
   int64_t capacity; /* instance capacity of bin/sort */
   /* pinned host slot the library copies num_rendered into */
   int32_t* num_rendered_pinned;
+  /* != 0: [ctrl] is clean -- all zero, or last used with the SAME P, W, H by an igs_forward /
+   * igs_forward_bin_render that returned IGS_OK or IGS_ERR_CAPACITY (the kernels put every counter
+   * back to zero when they are done with it) -- so the library skips its memset of [ctrl] (one
+   * stream operation less per frame) */
+  int32_t ctrl_clean;
 } IgsFwdArgs;
 
 typedef struct IgsBwdArgs {
@@ -143,6 +148,9 @@ typedef struct IgsBwdArgs {
   float* dL_dscales;    /* [P,3] */
   float* dL_drotations; /* [P,4] */
   float* dL_dextra_attrs; /* [P,ED] or NULL */
+  /* != 0: [accum] is clean -- all zero, or last used by an igs_backward that returned IGS_OK (the
+   * per-Gaussian kernel zeroes every row it has read) -- so the library skips its memset of [accum] */
+  int32_t accum_clean;
 } IgsBwdArgs;
 
 const char* igs_version(void);

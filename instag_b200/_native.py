@@ -30,6 +30,7 @@ class IgsFwdArgs(C.Structure):
         ("geom", _p), ("img", _p), ("bin", _p), ("sort", _p), ("ctrl", _p),
         ("capacity", C.c_int64),
         ("num_rendered_pinned", _p),
+        ("ctrl_clean", C.c_int32),
     ]
 
 
@@ -49,6 +50,7 @@ class IgsBwdArgs(C.Structure):
         ("dL_dmeans2D", _p), ("dL_dcolors", _p), ("dL_dopacity", _p), ("dL_dmeans3D", _p),
         ("dL_dcov3D", _p), ("dL_dnorm3D", _p), ("dL_dsh", _p), ("dL_dscales", _p),
         ("dL_drotations", _p), ("dL_dextra_attrs", _p),
+        ("accum_clean", C.c_int32),
     ]
 
 

@@ -233,7 +233,8 @@ int igs_forward(const IgsFwdArgs* a, igs_stream_t stream, int64_t* num_rendered)
   cudaStream_t s = (cudaStream_t)stream;
   const bool debug = a->debug != 0;
   if (num_rendered) *num_rendered = 0;
-  if (int r = reset_ctrl(a, s)) return r;
+  if (!a->ctrl_clean)
+    if (int r = reset_ctrl(a, s)) return r;
   if (a->P == 0) { // reference rasterize_points.cu:93: outputs stay at their fill value
     const size_t HW = (size_t)a->W * a->H;
     cudaMemsetAsync(a->out_depth, 0, HW * 4, s); cudaMemsetAsync(a->out_alpha, 0, HW * 4, s);
@@ -290,7 +291,8 @@ int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
   const ImgLayout il(a->W, a->H);
   const BinLayout bl(a->num_rendered);
   const char* g = (const char*)a->geom; const char* im = (const char*)a->img; const char* b = (const char*)a->bin;
-  if (int r = check_cuda(cudaMemsetAsync(a->accum, 0, accum_bytes(a->P, a->ED), s), "memset accum")) return r;
+  if (!a->accum_clean)
+    if (int r = check_cuda(cudaMemsetAsync(a->accum, 0, accum_bytes(a->P, a->ED), s), "memset accum")) return r;
 
   BwdRenderArgs ra{};
   ra.W = a->W; ra.H = a->H; ra.ED = a->ED;
@@ -326,7 +328,7 @@ int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
   pa.radii = a->radii;
   pa.splat = ra.splat;
   pa.clamped = (const uint8_t*)(g + gl.clamped);
-  pa.accum = ra.accum; pa.accum_extra = ra.accum_extra;
+  pa.accum = ra.accum; pa.accum_extra = ra.accum_extra; pa.ticket = ra.ticket;
   pa.dL_dmeans2D = a->dL_dmeans2D; pa.dL_dcolors = a->dL_dcolors; pa.dL_dopacity = a->dL_dopacity;
   pa.dL_dmeans3D = a->dL_dmeans3D; pa.dL_dcov3D = a->dL_dcov3D; pa.dL_dnorm3D = a->dL_dnorm3D;
   pa.dL_dsh = a->dL_dsh; pa.dL_dscales = a->dL_dscales; pa.dL_drotations = a->dL_drotations;

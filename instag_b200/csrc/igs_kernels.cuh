@@ -84,8 +84,9 @@ struct BwdPreArgs {
   const int32_t* radii;
   const float4* splat;
   const uint8_t* clamped;
-  const float* accum;
-  const float* accum_extra;
+  float* accum;        // read, then zeroed again (the next frame finds it clean)
+  float* accum_extra;
+  uint32_t* ticket;    // unit counter of the render-backward kernel, reset here
   float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dnorm3D, *dL_dsh;
   float *dL_dscales, *dL_drotations, *dL_dextra_attrs;
 };

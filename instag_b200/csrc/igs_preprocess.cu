@@ -244,9 +244,14 @@ __global__ void __launch_bounds__(PRE_THREADS, 2) preprocess_kernel(PreArgs a) {
   __threadfence();
   // (1) tile counts: one L2 round trip into shared memory (all requests in flight together);
   //     later phases read them from there.  Beyond HIST_SMEM_MAX_TILES they stay in L2.
+  //     The counters go back to zero as they are read: the next frame needs no memset of [ctrl].
   if (HIST_SMEM) {
-    for (int t = tid; t < T; t += PRE_THREADS) s_hist[t] = __ldcg(a.tile_count + (size_t)t * CNT_STRIDE);
+    for (int t = tid; t < T; t += PRE_THREADS) {
+      s_hist[t] = __ldcg(a.tile_count + (size_t)t * CNT_STRIDE);
+      a.tile_count[(size_t)t * CNT_STRIDE] = 0u;
+    }
   }
+  if (tid == 0) { a.header->done = 0u; a.header->render_ticket = 0u; }
 #define TILE_CNT(t) (HIST_SMEM ? s_hist[t] : __ldcg(a.tile_count + (size_t)(t) * CNT_STRIDE))
   // (2) CTA totals of tiles_touched -> exclusive prefixes (added to point_offsets by the
   //     duplicate kernel), num_rendered, overflow flag
@@ -336,6 +341,10 @@ __global__ void __launch_bounds__(PRE_THREADS, 2) preprocess_kernel(PreArgs a) {
   for (int t = t0; t < t1; t++) {
     const uint32_t slot = atomicAdd(&s_bucket[ORDER_BUCKET(TILE_CNT(t))], 1u);
     a.tile_order[slot] = (uint32_t)t;
+  }
+  if (!HIST_SMEM) { // the counts were read from global memory up to here
+    __syncthreads();
+    for (int t = tid; t < T; t += PRE_THREADS) a.tile_count[(size_t)t * CNT_STRIDE] = 0u;
   }
 #undef TILE_CNT
   PRE_MARK(6);

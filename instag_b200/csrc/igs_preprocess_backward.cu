@@ -137,9 +137,15 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(BwdPreArgs a) 
   const float* view = s_view;
   const float* proj = s_proj;
 
-  const float4* acc = reinterpret_cast<const float4*>(a.accum) + (size_t)idx * (ACC_F / 4);
-  float4 g0 = __ldg(acc), g1 = __ldg(acc + 1);
-  const float4 g2 = __ldg(acc + 2), g3 = __ldg(acc + 3);
+  if (idx == 0) *a.ticket = 0u; // the render-backward kernel is done with its unit counter
+  // the accumulator row is read once and put back to zero: the next backward needs no memset
+  float4* acc = reinterpret_cast<float4*>(a.accum) + (size_t)idx * (ACC_F / 4);
+  float4 g0 = acc[0], g1 = acc[1];
+  const float4 g2 = acc[2], g3 = acc[3];
+  {
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    acc[0] = z; acc[1] = z; acc[2] = z; acc[3] = z;
+  }
   const bool visible = __ldg(a.radii + idx) > 0;
   // The compositing backward leaves raw moments of g = G*dL/dalpha about the splat centre
   // (igs_common.cuh ACC_F); with dL/dG = opacity * dL/dalpha (reference backward.cu:690-709):
@@ -165,7 +171,11 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(BwdPreArgs a) 
   a.dL_dnorm3D[3 * idx] = g2.z; a.dL_dnorm3D[3 * idx + 1] = g2.w; a.dL_dnorm3D[3 * idx + 2] = g3.x;
   if (a.ED >= 1) {
     a.dL_dextra_attrs[(size_t)idx * a.ED] = g3.y;
-    for (int c = 1; c < a.ED; c++) a.dL_dextra_attrs[(size_t)idx * a.ED + c] = __ldg(a.accum_extra + (size_t)idx * (a.ED - 1) + c - 1);
+    for (int c = 1; c < a.ED; c++) {
+      float* e = a.accum_extra + (size_t)idx * (a.ED - 1) + c - 1;
+      a.dL_dextra_attrs[(size_t)idx * a.ED + c] = *e;
+      *e = 0.f;
+    }
   }
 
   float dmean[3] = {0.f, 0.f, 0.f}, dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};

@@ -36,6 +36,8 @@ class _DeviceScratch:
         self.capacity_hint = {}
         self.sizes = {}
         self.zero_imgs = {}
+        self.dirty = set()
+        self.ctrl_key = None
         # argument blocks are reused call after call (the library reads them before it returns)
         self.fwd_args, self.bwd_args = N.IgsFwdArgs(), N.IgsBwdArgs()
         self.fwd_args_ref, self.bwd_args_ref = C.byref(self.fwd_args), C.byref(self.bwd_args)
@@ -43,10 +45,18 @@ class _DeviceScratch:
         self.n_out_ref = C.byref(self.n_out)
 
     def buf(self, name, nbytes):
+        """Reusable scratch.  `ctrl` and `accum` are handed to the library zeroed and come back
+        clean from every successful call (the kernels put counters / rows back to zero), which the
+        C ABI's ctrl_clean / accum_clean flags tell it; `self.dirty` names the ones a failed call
+        may have left in an unknown state."""
         t = getattr(self, name)
         if t is None or t.numel() < nbytes:
-            t = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=self.device)
+            t = torch.zeros(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=self.device)
             setattr(self, name, t)
+            self.dirty.discard(name)
+        elif name in self.dirty:
+            t.zero_()
+            self.dirty.discard(name)
         return t
 
     def zeros_like_img(self, C_, H, W):
@@ -153,6 +163,9 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
     geom, img = state[:geom_bytes], state[geom_bytes:]
     binb = empty((lib.igs_bin_bytes(capacity),), dtype=torch.uint8, device=dev)
     sort = sc.buf("sort", lib.igs_sort_bytes(capacity))
+    if sc.ctrl_key != hint_key:  # another (P, H, W) lays [ctrl] out differently: what is clean for one is not for the other
+        sc.dirty.add("ctrl")
+        sc.ctrl_key = hint_key
     ctrl = sc.buf("ctrl", ctrl_bytes)
 
     keep = (_f32c(bg), _f32c(viewmatrix), _f32c(projmatrix), _f32c(campos), _f32c(means3D), _f32c(sh),
@@ -171,6 +184,8 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
     a.geom, a.img, a.bin, a.sort, a.ctrl = geom_ptr, geom_ptr + geom_bytes, binb.data_ptr(), sort.data_ptr(), ctrl.data_ptr()
     a.capacity = capacity
     a.num_rendered_pinned = sc.pinned_ptr
+    a.ctrl_clean = 1
+    sc.dirty.add("ctrl")  # until the call has returned without an exception
 
     n = sc.n_out
     with _on_device(dev):
@@ -183,6 +198,7 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
             st = lib.igs_forward_bin_render(sc.fwd_args_ref, stream)
         if st != N.IGS_OK:
             N.check(st, "forward")
+    sc.dirty.discard("ctrl")
     num_rendered = int(n.value)
     # next call with this shape: 25 % head-room over what this one needed
     sc.capacity_hint[hint_key] = max(int(num_rendered * 1.25) + 4096, 1 << 14)
@@ -260,6 +276,8 @@ def _backward_native(bg, means3D, radii, colors_precomp, scales, rotations, extr
      a.cov3Ds_precomp, a.norm3Ds_precomp, a.extra_attrs, a.radii, a.geom, a.img, a.bin, a.out_alpha,
      a.dL_dcolor, a.dL_ddepth, a.dL_dnorm, a.dL_dalpha, a.dL_dextra) = [_ptr(t) for t in keep]
     a.accum = accum.data_ptr()
+    a.accum_clean = 1
+    sc.dirty.add("accum")
     (a.dL_dmeans2D, a.dL_dcolors, a.dL_dopacity, a.dL_dmeans3D, a.dL_dcov3D, a.dL_dnorm3D, a.dL_dsh,
      a.dL_dscales, a.dL_drotations, a.dL_dextra_attrs) = [_ptr(t) for t in
                                                           (g_means2D, g_colors, g_opacity, g_means3D, g_cov3D,
@@ -268,6 +286,7 @@ def _backward_native(bg, means3D, radii, colors_precomp, scales, rotations, extr
         st = lib.igs_backward(sc.bwd_args_ref, stream)
         if st != N.IGS_OK:
             N.check(st, "backward")
+    sc.dirty.discard("accum")
     return g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_norm3D, g_sh, g_scales, g_rot, g_extra
 
 

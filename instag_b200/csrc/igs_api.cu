@@ -244,18 +244,40 @@ int igs_forward(const IgsFwdArgs* a, igs_stream_t stream, int64_t* num_rendered)
     return stage_check(debug, s, "empty forward");
   }
   const PreArgs pa = make_pre(a);
+  volatile int32_t* const slot = (volatile int32_t*)a->num_rendered_pinned;
+  if (pa.num_rendered_host) *slot = -1; // the preprocess kernel posts the count here (device-mapped pinned memory)
   prof_mark(0, s);
   launch_preprocess(pa, s);
   prof_mark(1, s);
   if (int r = stage_check(debug, s, "preprocess")) return r;
-  if (!pa.num_rendered_host) // slot not device-mapped: fall back to a copy-engine transfer
+  cudaEvent_t ev = g_event.get();
+  if (!pa.num_rendered_host) { // slot not device-mapped: a copy-engine transfer and an event right behind it
     if (int r = check_cuda(cudaMemcpyAsync(a->num_rendered_pinned, &pa.header->num_rendered, sizeof(int32_t),
                                            cudaMemcpyDeviceToHost, s), "copy num_rendered")) return r;
-  cudaEvent_t ev = g_event.get();
-  if (int r = check_cuda(cudaEventRecord(ev, s), "event record")) return r;
+    if (int r = check_cuda(cudaEventRecord(ev, s), "event record")) return r;
+  }
   // speculative second half: sized by capacity, bounded on the device by num_rendered
   if (int r = run_bin_render(a, s)) return r;
-  if (int r = check_cuda(cudaEventSynchronize(ev), "wait num_rendered")) return r;
+  if (!pa.num_rendered_host) {
+    if (int r = check_cuda(cudaEventSynchronize(ev), "wait num_rendered")) return r;
+  } else {
+    // Wait for the posted count itself, not for an event: nothing sits between the preprocess
+    // kernel and its dependents on the stream, and the host wakes when the store lands (the
+    // last preprocess CTA posts it before it builds the tile ranges).  The event behind the whole
+    // forward only guards against a kernel that died without posting.
+    if (int r = check_cuda(cudaEventRecord(ev, s), "event record")) return r;
+    for (unsigned spin = 1; *slot == -1; spin++) {
+      if ((spin & 0x3ff) == 0) {
+        const cudaError_t q = cudaEventQuery(ev);
+        if (q == cudaSuccess) break; // the forward is over; the count is there, or it never will be
+        if (q != cudaErrorNotReady) return check_cuda(q, "wait num_rendered");
+      }
+#if defined(__x86_64__) || defined(__i386__)
+      __builtin_ia32_pause();
+#endif
+    }
+    if (*slot == -1) { set_error("the preprocess kernel did not post num_rendered"); return IGS_ERR_CUDA; }
+  }
   const int64_t n = (int64_t)(uint32_t)*a->num_rendered_pinned;
   if (num_rendered) *num_rendered = n;
   if (n > a->capacity) {

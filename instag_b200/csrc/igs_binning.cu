@@ -80,6 +80,7 @@ __global__ void __launch_bounds__(DUP_THREADS) duplicate_kernel(BinArgs a) {
   const int g = blockIdx.x * DUP_THREADS + tid;
   if (HIST_SMEM)
     for (int t = tid; t < a.num_tiles; t += DUP_THREADS) s_slot[t] = 0u;
+  pdl_wait(); // everything below reads what the preprocess kernel wrote
   uint32_t n = 0, xy = 0, w = 1, depth = 0;
   if (g < a.P) {
     n = __ldg(a.tiles_touched + g);
@@ -142,6 +143,7 @@ __global__ void __launch_bounds__(TS_THREADS) tile_sort_kernel(BinArgs a) {
   __shared__ uint32_t s_part[TS_THREADS / 32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = blockIdx.x;
+  pdl_wait(); // the duplicate kernel's segments
   const uint2 range = a.ranges[tile];
   const int n = (int)(range.y - range.x);
   if (n == 0 || a.header->overflow) return;
@@ -251,11 +253,11 @@ void launch_binning(const BinArgs& a, cudaStream_t s) {
   if (a.P <= 0 || a.num_tiles <= 0) return;
   const int dup_blocks = (a.P + DUP_THREADS - 1) / DUP_THREADS;
   if (a.num_tiles <= HIST_SMEM_MAX_TILES)
-    duplicate_kernel<true><<<dup_blocks, DUP_THREADS, (size_t)a.num_tiles * sizeof(uint32_t), s>>>(a);
+    launch_after(duplicate_kernel<true>, dim3(dup_blocks), dim3(DUP_THREADS), (size_t)a.num_tiles * sizeof(uint32_t), s, a);
   else
-    duplicate_kernel<false><<<dup_blocks, DUP_THREADS, 0, s>>>(a);
+    launch_after(duplicate_kernel<false>, dim3(dup_blocks), dim3(DUP_THREADS), 0, s, a);
   prof_mark(2, s);
-  tile_sort_kernel<<<a.num_tiles, TS_THREADS, 0, s>>>(a);
+  launch_after(tile_sort_kernel, dim3(a.num_tiles), dim3(TS_THREADS), 0, s, a);
   prof_mark(3, s);
   prof_mark(4, s);
   count_launch(2);

@@ -138,6 +138,29 @@ constexpr int PROF_BOUNDARIES = 9;
 void prof_mark(int boundary, cudaStream_t s);
 void count_launch(int n = 1);
 
+// ---- programmatic dependent launch ------------------------------------------------
+// The kernels of a frame run back to back on one stream.  Each dependent kernel is launched with
+// the programmatic-stream-serialization attribute and starts with pdl_wait(): its launch is
+// processed while its predecessor still runs, its CTAs land on SMs as the predecessor's CTAs
+// retire, and they block in pdl_wait() until the predecessor grid has completed and its memory
+// is visible -- the launch latency between kernels disappears.  (In a kernel launched without
+// the attribute pdl_wait() returns immediately.)
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <class... KArgs, class... Args>
+inline cudaError_t launch_after(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                                Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
 // ---- device helpers ---------------------------------------------------------
 // a0*b0 + a1*b1 + a2*b2 with the contraction nvcc applies to that expression
 // (left product of the first sum fused, see DESIGN.md "FMA contraction");

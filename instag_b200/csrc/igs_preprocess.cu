@@ -284,7 +284,10 @@ __global__ void __launch_bounds__(PRE_THREADS, 2) preprocess_kernel(PreArgs a) {
       a.header->overflow = (int64_t)all > a.capacity ? 1u : 0u;
       // straight into the caller's pinned host slot: a 4-byte copy-engine transfer between two
       // kernels costs ~12 us of stream time on B200, a posted store costs nothing
-      if (a.num_rendered_host) *(volatile int32_t*)a.num_rendered_host = (int32_t)all;
+      if (a.num_rendered_host) {
+        *(volatile int32_t*)a.num_rendered_host = (int32_t)all;
+        __threadfence_system(); // the host polls this slot
+      }
     }
   }
   // (3) tile counts -> ranges and cursors

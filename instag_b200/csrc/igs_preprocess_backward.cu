@@ -131,6 +131,7 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(BwdPreArgs a) 
   const int tid = threadIdx.x;
   if (tid < 16) { s_view[tid] = __ldg(a.viewmatrix + tid); s_proj[tid] = __ldg(a.projmatrix + tid); }
   if (tid < 3) s_cam[tid] = __ldg(a.campos + tid);
+  pdl_wait(); // the accumulator rows of the render-backward kernel
   __syncthreads();
   const int idx = blockIdx.x * 256 + tid;
   if (idx >= a.P) return;
@@ -325,8 +326,8 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(BwdPreArgs a) 
 void launch_preprocess_backward(const BwdPreArgs& a, cudaStream_t s) {
   if (a.P <= 0) return;
   const int blocks = (a.P + 255) / 256;
-  if (a.shs) preprocess_backward_kernel<true><<<blocks, 256, 0, s>>>(a);
-  else preprocess_backward_kernel<false><<<blocks, 256, 0, s>>>(a);
+  if (a.shs) launch_after(preprocess_backward_kernel<true>, dim3(blocks), dim3(256), 0, s, a);
+  else launch_after(preprocess_backward_kernel<false>, dim3(blocks), dim3(256), 0, s, a);
   count_launch();
 }
 

@@ -64,6 +64,7 @@ __global__ void __launch_bounds__(RT) render_kernel(RenderArgs a) {
   __shared__ uint32_t s_id[ED_T < 0 ? RW : 1][32];
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  pdl_wait(); // the sorted tile lists
   if (a.header->overflow) return;
   const int num_units = a.grid_x * a.grid_y * 8;
   const int ED = ED_T < 0 ? a.ED : ED_T;
@@ -257,9 +258,9 @@ void launch_render(const RenderArgs& a, cudaStream_t s) {
                    capx = resident_ctas(render_kernel<-1>, RT);
   const int units = a.grid_x * a.grid_y * 8;
   const int want = (units + RW - 1) / RW;
-  if (a.ED == 0) render_kernel<0><<<min(want, cap0), RT, 0, s>>>(a);
-  else if (a.ED == 1) render_kernel<1><<<min(want, cap1), RT, 0, s>>>(a);
-  else render_kernel<-1><<<min(want, capx), RT, 0, s>>>(a);
+  if (a.ED == 0) launch_after(render_kernel<0>, dim3(min(want, cap0)), dim3(RT), 0, s, a);
+  else if (a.ED == 1) launch_after(render_kernel<1>, dim3(min(want, cap1)), dim3(RT), 0, s, a);
+  else launch_after(render_kernel<-1>, dim3(min(want, capx)), dim3(RT), 0, s, a);
   count_launch();
 }
 

@@ -261,15 +261,13 @@ int igs_forward(const IgsFwdArgs* a, igs_stream_t stream, int64_t* num_rendered)
   if (!pa.num_rendered_host) {
     if (int r = check_cuda(cudaEventSynchronize(ev), "wait num_rendered")) return r;
   } else {
-    // Wait for the posted count itself, not for an event: nothing sits between the preprocess
-    // kernel and its dependents on the stream, and the host wakes when the store lands (the
-    // last preprocess CTA posts it before it builds the tile ranges).  The event behind the whole
-    // forward only guards against a kernel that died without posting.
-    if (int r = check_cuda(cudaEventRecord(ev, s), "event record")) return r;
+    // Wait for the posted count itself, not for an event: nothing sits between the kernels on the
+    // stream, and the host wakes when the store lands (the last preprocess CTA posts it before it
+    // builds the tile ranges).  cudaStreamQuery only guards against a kernel that died without posting.
     for (unsigned spin = 1; *slot == -1; spin++) {
       if ((spin & 0x3ff) == 0) {
-        const cudaError_t q = cudaEventQuery(ev);
-        if (q == cudaSuccess) break; // the forward is over; the count is there, or it never will be
+        const cudaError_t q = cudaStreamQuery(s);
+        if (q == cudaSuccess) break; // the stream is idle; the count is there, or it never will be
         if (q != cudaErrorNotReady) return check_cuda(q, "wait num_rendered");
       }
 #if defined(__x86_64__) || defined(__i386__)

@@ -90,6 +90,7 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
   __shared__ float4 s_bm[2][32];
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  pdl_wait(); // whatever ran before on the stream (the forward, the caller's loss kernels) is complete
   const int num_units = a.grid_x * a.grid_y * 8;
   const int ED = ED_T < 0 ? a.ED : ED_T;
   const size_t HW = (size_t)a.H * a.W;
@@ -388,9 +389,9 @@ void launch_render_backward(const BwdRenderArgs& a, cudaStream_t s) {
                    capx = resident_ctas_bwd(render_backward_kernel<-1>, BT);
   const int units = a.grid_x * a.grid_y * 8;
   const int want = (units + BW - 1) / BW;
-  if (a.ED == 0) render_backward_kernel<0><<<min(want, cap0), BT, 0, s>>>(a);
-  else if (a.ED == 1) render_backward_kernel<1><<<min(want, cap1), BT, 0, s>>>(a);
-  else render_backward_kernel<-1><<<min(want, capx), BT, 0, s>>>(a);
+  if (a.ED == 0) launch_after(render_backward_kernel<0>, dim3(min(want, cap0)), dim3(BT), 0, s, a);
+  else if (a.ED == 1) launch_after(render_backward_kernel<1>, dim3(min(want, cap1)), dim3(BT), 0, s, a);
+  else launch_after(render_backward_kernel<-1>, dim3(min(want, capx)), dim3(BT), 0, s, a);
   count_launch();
 }
 

@@ -175,6 +175,10 @@ class Arm:
             self.host[o:o + n].copy_(self.t[k].reshape(-1).cpu())
         self.h2d_bytes = off * 4
         self.dev = [torch.empty(off, dtype=torch.float32, device=device) for _ in range(2)]
+        # the trainable leaves are views of the two device blocks, made once (as a model's parameters
+        # are); every step drops their .grad first (= optimizer.zero_grad(set_to_none=True))
+        self.leaves = [{name: blk[o:o + n].view(shape).detach().requires_grad_(True)
+                        for name, o, n, shape in self.blocks} for blk in self.dev]
         self.copy_stream = torch.cuda.Stream(device)
         self.ready = [torch.cuda.Event() for _ in range(2)]
         self.free = [torch.cuda.Event() for _ in range(2)]
@@ -210,8 +214,9 @@ class Arm:
         main = torch.cuda.current_stream(self.device)
         main.wait_event(self.ready[k])       # this step's inputs have arrived
         self._issue_copy(k ^ 1)              # next step's H2D, overlapped with this step's kernels
-        block = self.dev[k]
-        leaves = {name: block[o:o + n].view(shape).requires_grad_(True) for name, o, n, shape in self.blocks}
+        leaves = self.leaves[k]
+        for v in leaves.values():
+            v.grad = None
         m2 = torch.zeros_like(leaves["means3D"], requires_grad=True)
         color, depth, norm, alpha, radii, extra = self.Module(self.rs)(
             means3D=leaves["means3D"], means2D=m2, shs=leaves.get("shs"),

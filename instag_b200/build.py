@@ -77,5 +77,48 @@ def build(force=False, verbose=False):
     return LIB
 
 
+# ---- the compiled host side (csrc/igs_torch.cpp): a torch extension module linked against the library ----
+BINDING = os.path.join(HERE, "_igs_torch.so")
+BINDING_SRC = os.path.join(CSRC, "igs_torch.cpp")
+BINDING_STAMP = os.path.join(HERE, "_igs_torch.stamp")
+CXX = os.environ.get("CXX", "g++")
+
+
+def _binding_digest():
+    import hashlib
+    import torch
+    h = hashlib.sha256(torch.__version__.encode())
+    for p in (BINDING_SRC, os.path.join(HERE, "..", "include", "igs_raster.h")):
+        h.update(open(p, "rb").read())
+    return h.hexdigest()
+
+
+def build_binding(force=False):
+    """g++ build of _igs_torch.so (no nvcc: the file launches no kernel).  Links libigs_raster.so by
+    rpath $ORIGIN and torch's libraries, which `import torch` has already loaded."""
+    if not force and os.path.exists(BINDING) and os.path.exists(BINDING_STAMP) \
+            and open(BINDING_STAMP).read().strip() == _binding_digest():
+        return BINDING
+    import sysconfig
+    import torch
+    tdir = os.path.dirname(torch.__file__)
+    inc = [os.path.join(tdir, "include"), os.path.join(tdir, "include", "torch", "csrc", "api", "include"),
+           os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include"),
+           sysconfig.get_paths()["include"], os.path.join(HERE, "..", "include")]
+    cmd = [CXX, "-O2", "-std=c++17", "-fPIC", "-shared", "-fvisibility=hidden", "-Wno-attributes",
+           f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}",
+           "-DTORCH_EXTENSION_NAME=_igs_torch", "-DTORCH_API_INCLUDE_EXTENSION_H",
+           *[f"-I{i}" for i in inc], BINDING_SRC, "-o", BINDING,
+           f"-L{os.path.join(tdir, 'lib')}", "-lc10", "-lc10_cuda", "-ltorch_cpu", "-ltorch_cuda", "-ltorch",
+           "-ltorch_python", f"-L{HERE}", "-l:libigs_raster.so", "-Wl,-rpath,$ORIGIN"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"g++ failed on igs_torch.cpp:\n{r.stdout}\n{r.stderr}")
+    with open(BINDING_STAMP, "w") as f:
+        f.write(_binding_digest())
+    return BINDING
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_binding(force="--force" in sys.argv))

@@ -1,0 +1,301 @@
+// Compiled host side of the drop-in: the autograd node of the rasterizer as a C++
+// torch::autograd::Function over the C ABI of libigs_raster (include/igs_raster.h).
+//
+// Role in the reference ("DGR" = submodules/diff-gaussian-rasterization): the torch binding
+// rasterize_points.cu:35-239 (RasterizeGaussiansCUDA / RasterizeGaussiansBackwardCUDA) plus the
+// autograd.Function of diff_gauss/__init__.py:52-178.  The Python twin of this file is
+// instag_b200/rasterizer.py (_forward_native / _backward_native / _RasterizeGaussians); both call
+// the same kernels.  This one exists because an end-to-end step of the C2 workload is host bound:
+// allocations, argument marshalling and the backward node cost ~150 us per step from Python and
+// ~30 us from here (the backward also runs on the autograd engine's thread without the GIL).
+//
+// No kernel is launched from this file and there is no fallback: every entry point ends in
+// igs_forward / igs_backward.
+#include <torch/extension.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <c10/cuda/CUDAStream.h>
+
+#include <array>
+#include <map>
+#include <mutex>
+#include <tuple>
+
+#include "igs_raster.h"
+
+namespace {
+
+using at::Tensor;
+using torch::autograd::AutogradContext;
+using torch::autograd::variable_list;
+
+// Reusable buffers of one (device, stream, host thread); see rasterizer.py::_DeviceScratch.
+struct Scratch {
+  Tensor sort, ctrl, accum, pinned;
+  bool ctrl_dirty = false, accum_dirty = false;
+  std::tuple<int64_t, int64_t, int64_t> ctrl_key{-1, -1, -1};
+  std::map<std::tuple<int64_t, int64_t, int64_t>, int64_t> capacity_hint;
+  std::map<std::tuple<int64_t, int64_t, int64_t>, Tensor> zero_imgs;
+
+  // `ctrl` and `accum` are handed to the library zeroed and come back clean from every successful
+  // call; a failed call marks them dirty and they are cleared before the next one.
+  Tensor& buf(Tensor& t, bool& dirty, size_t nbytes, const at::Device& dev, bool zeroed) {
+    if (!t.defined() || (size_t)t.numel() < nbytes) {
+      auto opt = at::TensorOptions().dtype(at::kByte).device(dev);
+      int64_t n = (int64_t)(nbytes + nbytes / 4) + 256;
+      t = zeroed ? at::zeros({n}, opt) : at::empty({n}, opt);
+      dirty = false;
+    } else if (dirty) {
+      t.zero_();
+      dirty = false;
+    }
+    return t;
+  }
+  const Tensor& zero_img(int64_t C, int64_t H, int64_t W, const at::Device& dev) {
+    auto key = std::make_tuple(C, H, W);
+    auto it = zero_imgs.find(key);
+    if (it == zero_imgs.end())
+      it = zero_imgs.emplace(key, at::zeros({C, H, W}, at::TensorOptions().dtype(at::kFloat).device(dev))).first;
+    return it->second;
+  }
+};
+
+Scratch& scratch(int device, cudaStream_t stream) {
+  // never destroyed: the tensors must not outlive the CUDA context at thread / process exit
+  thread_local auto* all = new std::map<std::pair<int, cudaStream_t>, Scratch>();
+  Scratch& s = (*all)[{device, stream}];
+  if (!s.pinned.defined()) s.pinned = at::zeros({4}, at::kInt).pin_memory();
+  return s;
+}
+
+inline Tensor f32c(const Tensor& t) {
+  Tensor r = t.scalar_type() == at::kFloat ? t : t.to(at::kFloat);
+  return r.is_contiguous() ? r : r.contiguous();
+}
+inline const float* fptr(const Tensor& t) { return t.numel() ? t.data_ptr<float>() : nullptr; }
+inline float* fptr_mut(Tensor& t) { return t.numel() ? t.data_ptr<float>() : nullptr; }
+
+[[noreturn]] void fail(int st, const char* what) {
+  TORCH_CHECK(false, "libigs_raster ", what, " failed (", st, "): ", igs_last_error());
+}
+
+// Packed gradient block: same layout as rasterizer.py::gradient_layout (parameter gradients first,
+// every block 16-byte aligned).  Return order: means2D, colours, opacity, means3D, cov3D, norm3D,
+// sh, scales, rotations, extra.
+struct GradLayout {
+  std::array<int64_t, 10> start, width;
+  int64_t total;
+};
+GradLayout gradient_layout(int64_t P, int64_t M, int64_t ED) {
+  GradLayout g;
+  g.width = {3, 3, 1, 3, 6, 3, 3 * M, 3, 4, ED};
+  static const int order[10] = {3, 1, 2, 6, 7, 8, 9, 0, 4, 5};
+  int64_t o = 0;
+  for (int i : order) {
+    g.start[i] = o;
+    o += (P * g.width[i] + 3) / 4 * 4;
+  }
+  g.total = o;
+  return g;
+}
+
+// Optional allocator of the packed gradient block (sharding.NvlsGradientBlock puts it in NVLink
+// multicast memory): a Python callable fn(n_floats, device) -> flat float32 tensor.
+py::object* g_grad_alloc = new py::object();  // leaked on purpose (no Python at static destruction)
+std::mutex g_grad_alloc_mutex;
+bool g_have_grad_alloc = false;
+
+struct RasterizeFn : public torch::autograd::Function<RasterizeFn> {
+  static variable_list forward(AutogradContext* ctx, const Tensor& means3D, const Tensor& means2D, const Tensor& sh,
+                               const Tensor& colors_precomp, const Tensor& opacities, const Tensor& scales,
+                               const Tensor& rotations, const Tensor& cov3Ds_precomp, const Tensor& norm3Ds_precomp,
+                               const Tensor& extra_attrs, const Tensor& bg, const Tensor& viewmatrix,
+                               const Tensor& projmatrix, const Tensor& campos, double tanfovx, double tanfovy,
+                               double scale_modifier, int64_t H, int64_t W, int64_t sh_degree, bool prefiltered,
+                               bool fuse_normalize) {
+    (void)means2D;
+    TORCH_CHECK(means3D.dim() == 2 && means3D.size(1) == 3, "means3D must have dimensions (num_points, 3)");
+    TORCH_CHECK(means3D.is_cuda(), "libigs_raster is CUDA-only: means3D must be a CUDA tensor (no CPU fallback)");
+    TORCH_CHECK(extra_attrs.size(0) == 0 || extra_attrs.size(1) <= IGS_MAX_EXTRA_DIMS, "too many extra attributes");
+    const at::Device dev = means3D.device();
+    c10::cuda::CUDAGuard guard(dev);
+    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+    Scratch& sc = scratch(dev.index(), stream);
+    const int64_t P = means3D.size(0);
+    const int64_t M = sh.numel() ? sh.size(1) : 0;
+    const int64_t ED = extra_attrs.size(0) != 0 ? extra_attrs.size(1) : 0;
+    auto f32 = at::TensorOptions().dtype(at::kFloat).device(dev);
+    auto u8 = at::TensorOptions().dtype(at::kByte).device(dev);
+
+    Tensor color = at::empty({3, H, W}, f32), depth = at::empty({1, H, W}, f32), norm = at::empty({3, H, W}, f32),
+           alpha = at::empty({1, H, W}, f32);
+    Tensor extra = ED > 0 ? at::empty({ED, H, W}, f32) : at::empty({0}, f32);
+    Tensor radii = at::empty({P}, at::TensorOptions().dtype(at::kInt).device(dev));
+
+    const auto key = std::make_tuple(P, H, W);
+    const size_t geom_bytes = igs_geom_bytes((int32_t)P), img_bytes = igs_img_bytes((int32_t)W, (int32_t)H);
+    auto hint = sc.capacity_hint.find(key);
+    int64_t capacity = hint != sc.capacity_hint.end() ? hint->second : std::max<int64_t>(8 * P, 1 << 16);
+    // forward state kept for backward: one allocation, [geom | img]
+    Tensor state = at::empty({(int64_t)(geom_bytes + img_bytes)}, u8);
+    Tensor binb = at::empty({(int64_t)igs_bin_bytes(capacity)}, u8);
+    bool no_dirt = false;
+    Tensor& sort = sc.buf(sc.sort, no_dirt, igs_sort_bytes(capacity), dev, false);
+    if (sc.ctrl_key != key) {  // another (P, H, W) lays [ctrl] out differently
+      sc.ctrl_dirty = true;
+      sc.ctrl_key = key;
+    }
+    Tensor& ctrl = sc.buf(sc.ctrl, sc.ctrl_dirty, igs_ctrl_bytes((int32_t)P, (int32_t)W, (int32_t)H), dev, true);
+
+    Tensor k_bg = f32c(bg), k_view = f32c(viewmatrix), k_proj = f32c(projmatrix), k_cam = f32c(campos),
+           k_means = f32c(means3D), k_sh = f32c(sh), k_col = f32c(colors_precomp), k_op = f32c(opacities),
+           k_sc = f32c(scales), k_rot = f32c(rotations), k_cov = f32c(cov3Ds_precomp), k_n3 = f32c(norm3Ds_precomp),
+           k_ex = f32c(extra_attrs);
+    IgsFwdArgs a = {};
+    a.P = (int32_t)P, a.D = (int32_t)sh_degree, a.M = (int32_t)M, a.ED = (int32_t)ED, a.W = (int32_t)W, a.H = (int32_t)H;
+    a.tan_fovx = (float)tanfovx, a.tan_fovy = (float)tanfovy, a.scale_modifier = (float)scale_modifier;
+    a.prefiltered = prefiltered, a.debug = 0, a.normalize_norm = fuse_normalize;
+    a.bg = fptr(k_bg), a.viewmatrix = fptr(k_view), a.projmatrix = fptr(k_proj), a.campos = fptr(k_cam);
+    a.means3D = fptr(k_means), a.shs = fptr(k_sh), a.colors_precomp = fptr(k_col), a.opacities = fptr(k_op);
+    a.scales = fptr(k_sc), a.rotations = fptr(k_rot), a.cov3Ds_precomp = fptr(k_cov), a.norm3Ds_precomp = fptr(k_n3);
+    a.extra_attrs = fptr(k_ex);
+    a.out_color = color.data_ptr<float>(), a.out_depth = depth.data_ptr<float>(), a.out_norm = norm.data_ptr<float>();
+    a.out_alpha = alpha.data_ptr<float>(), a.out_extra = fptr_mut(extra);
+    a.radii = P > 0 ? radii.data_ptr<int32_t>() : nullptr;
+    uint8_t* st_ptr = state.data_ptr<uint8_t>();
+    a.geom = st_ptr, a.img = st_ptr + geom_bytes, a.bin = binb.data_ptr(), a.sort = sort.data_ptr(), a.ctrl = ctrl.data_ptr();
+    a.capacity = capacity;
+    a.num_rendered_pinned = sc.pinned.data_ptr<int32_t>();
+    a.ctrl_clean = 1;
+    sc.ctrl_dirty = true;  // until the call has returned without an error
+
+    int64_t num_rendered = 0;
+    int st = igs_forward(&a, stream, &num_rendered);
+    if (st == IGS_ERR_CAPACITY) {
+      capacity = (int64_t)(num_rendered * 1.1) + 4096;
+      binb = at::empty({(int64_t)igs_bin_bytes(capacity)}, u8);
+      Tensor& sort2 = sc.buf(sc.sort, no_dirt, igs_sort_bytes(capacity), dev, false);
+      a.bin = binb.data_ptr(), a.sort = sort2.data_ptr(), a.capacity = capacity;
+      st = igs_forward_bin_render(&a, stream);
+    }
+    if (st != IGS_OK) fail(st, "forward");
+    sc.ctrl_dirty = false;
+    sc.capacity_hint[key] = std::max<int64_t>((int64_t)(num_rendered * 1.25) + 4096, 1 << 14);
+
+    ctx->saved_data["num_rendered"] = num_rendered;
+    ctx->saved_data["tanfovx"] = tanfovx;
+    ctx->saved_data["tanfovy"] = tanfovy;
+    ctx->saved_data["scale_modifier"] = scale_modifier;
+    ctx->saved_data["sh_degree"] = sh_degree;
+    ctx->saved_data["fused_norm"] = fuse_normalize;
+    ctx->set_materialize_grads(false);
+    ctx->mark_non_differentiable({radii});
+    ctx->save_for_backward({colors_precomp, means3D, scales, rotations, cov3Ds_precomp, norm3Ds_precomp, radii,
+                            extra_attrs, sh, state, binb, alpha, bg, viewmatrix, projmatrix, campos,
+                            fuse_normalize ? norm : Tensor()});
+    return {color, depth, norm, alpha, radii, extra};
+  }
+
+  static variable_list backward(AutogradContext* ctx, variable_list grad_out) {
+    const auto saved = ctx->get_saved_variables();
+    const Tensor &colors_precomp = saved[0], &means3D = saved[1], &scales = saved[2], &rotations = saved[3],
+                 &cov3Ds_precomp = saved[4], &norm3Ds_precomp = saved[5], &radii = saved[6], &extra_attrs = saved[7],
+                 &sh = saved[8], &state = saved[9], &binb = saved[10], &alpha = saved[11], &bg = saved[12],
+                 &viewmatrix = saved[13], &projmatrix = saved[14], &campos = saved[15], &norm_out = saved[16];
+    const bool fused_norm = ctx->saved_data["fused_norm"].toBool();
+    const at::Device dev = means3D.device();
+    c10::cuda::CUDAGuard guard(dev);
+    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+    Scratch& sc = scratch(dev.index(), stream);
+    const int64_t P = means3D.size(0), H = alpha.size(1), W = alpha.size(2);
+    const int64_t ED = extra_attrs.numel() ? extra_attrs.size(1) : 0;
+    const int64_t M = sh.numel() ? sh.size(1) : 0;
+    auto f32 = at::TensorOptions().dtype(at::kFloat).device(dev);
+
+    const GradLayout lay = gradient_layout(P, M, ED);
+    Tensor flat;
+    if (g_have_grad_alloc) {
+      py::gil_scoped_acquire gil;
+      std::lock_guard<std::mutex> lock(g_grad_alloc_mutex);
+      if (g_have_grad_alloc)
+        flat = (*g_grad_alloc)(lay.total, py::cast(dev)).cast<Tensor>();
+    }
+    if (!flat.defined()) flat = at::empty({lay.total}, f32);
+    std::array<Tensor, 10> g;
+    for (int i = 0; i < 10; ++i) g[i] = flat.narrow(0, lay.start[i], P * lay.width[i]).view({P, lay.width[i]});
+    g[6] = g[6].view({P, M, 3});
+    if (ED == 0) g[9] = at::empty(extra_attrs.sizes(), f32);  // no elements; the shape autograd expects
+    Tensor& accum = sc.buf(sc.accum, sc.accum_dirty, igs_accum_bytes((int32_t)P, (int32_t)ED), dev, true);
+
+    auto grad = [&](const Tensor& t, int64_t C) { return t.defined() ? f32c(t) : sc.zero_img(C, H, W, dev); };
+    Tensor k_bg = f32c(bg), k_view = f32c(viewmatrix), k_proj = f32c(projmatrix), k_cam = f32c(campos),
+           k_means = f32c(means3D), k_sh = f32c(sh), k_col = f32c(colors_precomp), k_sc = f32c(scales),
+           k_rot = f32c(rotations), k_cov = f32c(cov3Ds_precomp), k_n3 = f32c(norm3Ds_precomp),
+           k_ex = f32c(extra_attrs), k_alpha = f32c(alpha);
+    Tensor d_color = grad(grad_out[0], 3), d_depth = grad(grad_out[1], 1), d_norm = grad(grad_out[2], 3),
+           d_alpha = grad(grad_out[3], 1), d_extra = ED > 0 ? grad(grad_out[5], ED) : Tensor();
+    Tensor k_norm = fused_norm ? f32c(norm_out) : Tensor();
+
+    IgsBwdArgs a = {};
+    a.P = (int32_t)P, a.D = (int32_t)ctx->saved_data["sh_degree"].toInt(), a.M = (int32_t)M, a.ED = (int32_t)ED;
+    a.W = (int32_t)W, a.H = (int32_t)H;
+    a.tan_fovx = (float)ctx->saved_data["tanfovx"].toDouble(), a.tan_fovy = (float)ctx->saved_data["tanfovy"].toDouble();
+    a.scale_modifier = (float)ctx->saved_data["scale_modifier"].toDouble();
+    a.debug = 0, a.normalize_norm = fused_norm;
+    a.num_rendered = ctx->saved_data["num_rendered"].toInt();
+    a.bg = fptr(k_bg), a.viewmatrix = fptr(k_view), a.projmatrix = fptr(k_proj), a.campos = fptr(k_cam);
+    a.means3D = fptr(k_means), a.shs = fptr(k_sh), a.colors_precomp = fptr(k_col), a.scales = fptr(k_sc);
+    a.rotations = fptr(k_rot), a.cov3Ds_precomp = fptr(k_cov), a.norm3Ds_precomp = fptr(k_n3), a.extra_attrs = fptr(k_ex);
+    a.radii = radii.numel() ? radii.data_ptr<int32_t>() : nullptr;
+    const uint8_t* st_ptr = state.data_ptr<uint8_t>();
+    a.geom = st_ptr, a.img = st_ptr + igs_geom_bytes((int32_t)P), a.bin = binb.data_ptr();
+    a.out_alpha = fptr(k_alpha), a.out_norm = fused_norm ? fptr(k_norm) : nullptr;
+    a.dL_dcolor = fptr(d_color), a.dL_ddepth = fptr(d_depth), a.dL_dnorm = fptr(d_norm), a.dL_dalpha = fptr(d_alpha);
+    a.dL_dextra = ED > 0 ? fptr(d_extra) : nullptr;
+    a.accum = accum.data_ptr();
+    a.accum_clean = 1;
+    sc.accum_dirty = true;
+    a.dL_dmeans2D = fptr_mut(g[0]), a.dL_dcolors = fptr_mut(g[1]), a.dL_dopacity = fptr_mut(g[2]);
+    a.dL_dmeans3D = fptr_mut(g[3]), a.dL_dcov3D = fptr_mut(g[4]), a.dL_dnorm3D = fptr_mut(g[5]);
+    a.dL_dsh = fptr_mut(g[6]), a.dL_dscales = fptr_mut(g[7]), a.dL_drotations = fptr_mut(g[8]);
+    a.dL_dextra_attrs = fptr_mut(g[9]);
+    int st = igs_backward(&a, stream);
+    if (st != IGS_OK) fail(st, "backward");
+    sc.accum_dirty = false;
+
+    // forward's argument order: means3D, means2D, sh, colours, opacities, scales, rotations, cov3D,
+    // norm3D, extra, then 12 non-differentiable settings.  Gradients nobody asked for (including
+    // those of the empty 'None' sentinels) are dropped, as autograd does with the reference's.
+    static const int src[10] = {3, 0, 6, 1, 2, 7, 8, 4, 5, 9};
+    variable_list out(22);
+    for (int i = 0; i < 10; ++i)
+      if (ctx->needs_input_grad(i)) out[i] = g[src[i]];
+    return out;
+  }
+};
+
+std::vector<Tensor> rasterize(const Tensor& means3D, const Tensor& means2D, const Tensor& sh, const Tensor& colors_precomp,
+                              const Tensor& opacities, const Tensor& scales, const Tensor& rotations,
+                              const Tensor& cov3Ds_precomp, const Tensor& norm3Ds_precomp, const Tensor& extra_attrs,
+                              const Tensor& bg, const Tensor& viewmatrix, const Tensor& projmatrix, const Tensor& campos,
+                              double tanfovx, double tanfovy, double scale_modifier, int64_t H, int64_t W,
+                              int64_t sh_degree, bool prefiltered, bool fuse_normalize) {
+  return RasterizeFn::apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                            norm3Ds_precomp, extra_attrs, bg, viewmatrix, projmatrix, campos, tanfovx, tanfovy,
+                            scale_modifier, H, W, sh_degree, prefiltered, fuse_normalize);
+}
+
+void set_gradient_allocator(py::object fn) {
+  std::lock_guard<std::mutex> lock(g_grad_alloc_mutex);
+  g_have_grad_alloc = !fn.is_none();
+  *g_grad_alloc = g_have_grad_alloc ? fn : py::object();
+}
+
+}  // namespace
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+  m.doc() = "autograd node of the libigs_raster rasterizer (C++ host side over the C ABI)";
+  m.def("rasterize", &rasterize, py::call_guard<py::gil_scoped_release>(),
+        "forward of the rasterizer as one autograd node: (color, depth, norm, alpha, radii, extra)");
+  m.def("set_gradient_allocator", &set_gradient_allocator, "fn(n_floats, device) -> flat float32 tensor, or None");
+  m.def("library_version", []() { return std::string(igs_version()); });
+}

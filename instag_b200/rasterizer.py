@@ -8,6 +8,7 @@ runs unmodified.  PyTorch supplies device memory, streams and autograd; every
 kernel is in libigs_raster.so (no fallback path exists).
 """
 import ctypes as C
+import os
 import threading
 from typing import NamedTuple
 
@@ -231,7 +232,36 @@ _grad_alloc = None
 def set_gradient_allocator(fn):
     global _grad_alloc
     prev, _grad_alloc = _grad_alloc, fn
+    if _host_binding is not None or host_path() == "cxx":
+        binding().set_gradient_allocator(fn)
     return prev
+
+
+# ---- the compiled twin of _forward_native / _backward_native / _RasterizeGaussians ----
+_host_binding = None
+
+
+def host_path():
+    """Which host side runs the autograd node: "cxx" (csrc/igs_torch.cpp, the default) or "python"
+    (this file; IGS_HOST=python, and always with raster_settings.debug, whose snapshot dumps live
+    here).  Both end in the same igs_forward / igs_backward calls."""
+    return os.environ.get("IGS_HOST", "cxx")
+
+
+def binding():
+    """The torch extension module built from csrc/igs_torch.cpp; raises when it has not been built."""
+    global _host_binding
+    if _host_binding is None:
+        N.lib()  # libigs_raster.so first: the extension links against it
+        try:
+            from . import _igs_torch
+        except ImportError as ex:
+            raise RuntimeError("instag_b200/_igs_torch.so is missing or does not load: build it with "
+                               "`python -m instag_b200.build` (or run with IGS_HOST=python)") from ex
+        _host_binding = _igs_torch
+        if _grad_alloc is not None:
+            _igs_torch.set_gradient_allocator(_grad_alloc)
+    return _host_binding
 
 
 def _backward_native(bg, means3D, radii, colors_precomp, scales, rotations, extra_attrs, scale_modifier,
@@ -255,7 +285,7 @@ def _backward_native(bg, means3D, radii, colors_precomp, scales, rotations, extr
     (g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_norm3D, g_sh, g_scales, g_rot, g_extra) = outs
     g_sh = g_sh.view(P, M, 3)
     if ED == 0:
-        g_extra = torch.empty((0,), dtype=torch.float32, device=dev)
+        g_extra = torch.empty(tuple(extra_attrs.shape), dtype=torch.float32, device=dev)  # no elements
     accum = sc.buf("accum", lib.igs_accum_bytes(P, ED))
 
     def grad(t, C_):
@@ -369,9 +399,28 @@ class _RasterizeGaussiansUnitNormal(_RasterizeGaussians):
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                         norm3Ds_precomp, extra_attrs, raster_settings):
     # DGR diff_gauss/__init__.py:21-50; the F.normalize of :48 is fused into the kernels
+    rs = raster_settings
+    if not rs.debug and host_path() == "cxx":
+        return tuple(binding().rasterize(
+            means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, norm3Ds_precomp,
+            extra_attrs, rs.bg, rs.viewmatrix, rs.projmatrix, rs.campos, float(rs.tanfovx), float(rs.tanfovy),
+            float(rs.scale_modifier), int(rs.image_height), int(rs.image_width), int(rs.sh_degree),
+            bool(rs.prefiltered), True))
     return _RasterizeGaussiansUnitNormal.apply(
         means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, norm3Ds_precomp,
         extra_attrs, raster_settings)
+
+
+_NONE = None
+
+
+def _none_tensor():
+    """The reference's stand-in for an absent input, `torch.Tensor([])` (DGR diff_gauss/__init__.py:
+    232-246); it is only ever read for its emptiness, so one instance serves every call."""
+    global _NONE
+    if _NONE is None:
+        _NONE = torch.Tensor([])
+    return _NONE
 
 
 class GaussianRasterizer(nn.Module):
@@ -405,18 +454,18 @@ class GaussianRasterizer(nn.Module):
                 ((scales is not None or rotations is not None) and cov3Ds_precomp is not None):
             raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
         if shs is None:
-            shs = torch.Tensor([])
+            shs = _none_tensor()
         if colors_precomp is None:
-            colors_precomp = torch.Tensor([])
+            colors_precomp = _none_tensor()
         if scales is None:
             raise ValueError('To support norm and depth prediction, scales == None is not allowed')
         if rotations is None:
             raise ValueError('To support norm and depth prediction, rotations == None is not allowed')
         if cov3Ds_precomp is None:
-            cov3Ds_precomp = torch.Tensor([])
+            cov3Ds_precomp = _none_tensor()
         if norm3Ds_precomp is None:
-            norm3Ds_precomp = torch.Tensor([])
+            norm3Ds_precomp = _none_tensor()
         if extra_attrs is None:
-            extra_attrs = torch.Tensor([])
+            extra_attrs = _none_tensor()
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
                                    cov3Ds_precomp, norm3Ds_precomp, extra_attrs, raster_settings)

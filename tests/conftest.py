@@ -43,6 +43,7 @@ def _built():
     oracle once per session; both are no-ops when the outputs are fresh."""
     from instag_b200 import build as B
     B.build()
+    B.build_binding()
     if not os.path.exists(os.path.join(ROOT, "oracle", "liboracle_cpu.so")):
         subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "cpu"])
     yield

@@ -93,3 +93,29 @@ def test_missing_library_raises(monkeypatch):
     monkeypatch.setattr(N, "LIB_PATH", "/nonexistent/libigs_raster.so")
     with pytest.raises(RuntimeError, match="no CPU or PyTorch fallback"):
         N.lib()
+
+
+def test_compiled_host_side_loads_and_rejects_cpu_tensors():
+    """csrc/igs_torch.cpp (the autograd node in C++) imports without a GPU, links the same library
+    and, like the Python host side, refuses anything that is not on a CUDA device."""
+    import pytest
+    import torch
+    from instag_b200 import rasterizer as R
+    b = R.binding()
+    assert b.library_version() == N.lib().igs_version().decode()
+    e = torch.Tensor([])
+    m = torch.zeros(4, 3)
+    with pytest.raises(RuntimeError, match="CUDA-only"):
+        b.rasterize(m, m, e, m, torch.zeros(4, 1), m, torch.zeros(4, 4), e, e, e, torch.zeros(3), torch.eye(4),
+                    torch.eye(4), torch.zeros(3), 0.5, 0.5, 1.0, 16, 16, 0, False, True)
+    with pytest.raises(RuntimeError, match=r"means3D must have dimensions \(num_points, 3\)"):
+        b.rasterize(torch.zeros(4, 2), m, e, m, torch.zeros(4, 1), m, torch.zeros(4, 4), e, e, e, torch.zeros(3),
+                    torch.eye(4), torch.eye(4), torch.zeros(3), 0.5, 0.5, 1.0, 16, 16, 0, False, True)
+
+
+def test_host_path_switch(monkeypatch):
+    from instag_b200 import rasterizer as R
+    monkeypatch.delenv("IGS_HOST", raising=False)
+    assert R.host_path() == "cxx"
+    monkeypatch.setenv("IGS_HOST", "python")
+    assert R.host_path() == "python"

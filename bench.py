@@ -520,32 +520,49 @@ def synth_fps(torch, dist, world, rank, flush, device, frames=60):
     cams = [all_cams[i] for i in SHD.shard_indices(frames * world, rank, world)]
     clouds = [S.make_cloud(100_000, sh_degree=1, M=4, seed=0), S.make_cloud(30_000, sh_degree=1, M=4, seed=1)]
     tcl = [U.to_torch(c, device) for c in clouds]
+    # through the module API, as render_motion / render_motion_mouth_con call it (gaussian_renderer/
+    # __init__.py:241-251, 413-423), under no_grad as synthesize_fuse.py does
+    from diff_gauss import GaussianRasterizer
+    m2 = [torch.zeros_like(cl["means3D"]) for cl in tcl]
     scenes = []
     for cam in cams:
         tc = U.to_torch(dict(cam, bg=np.zeros(3, np.float32)), device)
-        scenes.append([U.raw_args_fwd({**cl, **tc}) for cl in tcl])
+        scenes.append([U.settings_from({**cl, **tc}) for cl in tcl])
     it = iter(range(10 ** 9))
     from instag_b200 import synthesis as SY
     ring = SY.FrameRing(512, 512, depth=8, device=device)
     bgimg = torch.full((3, 512, 512), 127.0, device=device)
 
+    pair = SY.PairOverlap(device)  # the mouth pass on a side stream, under the face pass
+
+    def render(k):
+        cl = tcl[k]
+
+        def fn(i):
+            o = GaussianRasterizer(scenes[i][k])(
+                means3D=cl["means3D"], means2D=m2[k], shs=cl["shs"], opacities=cl["opacities"], scales=cl["scales"],
+                rotations=cl["rotations"], extra_attrs=cl.get("extra_attrs"))
+            return {"render": o[0], "alpha": o[3]}
+        return fn
+    render_face, render_mouth = render(0), render(1)
+
     def step():
         i = next(it) % len(scenes)
-        face = R._forward_native(*scenes[i][0])
-        mouth = R._forward_native(*scenes[i][1])
+        face, mouth = pair(render_face, render_mouth, i)
         # synthesize_fuse.py:64-76: one compose kernel into a ring slot, asynchronous D2H of the uint8 frame
         if ring.full():
             ring.collect(block=True)
-        SY.compose_frame(face[1], face[4], mouth[1], mouth[4], bgimg, out=ring.slot())
+        SY.compose_frame(face["render"], face["alpha"], mouth["render"], mouth["alpha"], bgimg, out=ring.slot())
         ring.commit(i)
         ring.collect()
         return None
 
-    ms, _, _ = timed(torch, dist, step, frames, 5, flush, world)
+    with torch.no_grad():
+        ms, _, _ = timed(torch, dist, step, frames, 5, flush, world)
     ring.collect(block=True)
     return {"value": world * 1000.0 / ms, "unit": "frames/s", "ms_per_frame": ms,
-            "workload": "face 100k + mouth 30k Gaussians (SH deg 1, M=4), 512x512, forward only + fused compose "
-                        "(igs_compose_frame) into a device ring, uint8 frames copied to pinned memory on a side "
+            "workload": "face 100k + mouth 30k Gaussians (SH deg 1, M=4), 512x512, forward only (the two passes "
+                        "of a frame on two streams) + fused compose (igs_compose_frame) into a device ring, uint8 frames copied to pinned memory on a side "
                         "stream; frames sharded over ranks, no collective"}
 
 

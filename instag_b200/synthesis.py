@@ -105,17 +105,48 @@ class FrameRing:
         return self.head - self.tail >= self.depth
 
 
+class PairOverlap:
+    """Runs the mouth pass of a frame on a side stream while the face pass runs on the current one.
+
+    The two rasterizations of a frame (synthesize_fuse.py:57-58) do not read each other's results,
+    and the front of each (per-Gaussian pass, binning, per-tile sort) leaves most of the GPU idle,
+    so the two overlap well.  Only for callbacks that are independent on the device: the side
+    stream sees everything queued before the frame, nothing queued by the face pass of this frame.
+    The library keeps its scratch per (device, stream), so the two passes share no workspace."""
+
+    def __init__(self, device):
+        self.side = torch.cuda.Stream(device)
+        self.fork, self.join = torch.cuda.Event(), torch.cuda.Event()
+
+    def __call__(self, render_face, render_mouth, view):
+        main = torch.cuda.current_stream()
+        self.fork.record(main)
+        self.side.wait_event(self.fork)
+        # mouth first (measured: 265 us per frame; face first 286; serial 279): the short pass is
+        # in its render kernel while the host queues the face pass behind its own instance count
+        with torch.cuda.stream(self.side):
+            mouth = render_mouth(view)
+            self.join.record(self.side)
+        face = render_face(view)
+        main.wait_event(self.join)
+        for t in (mouth["render"], mouth["alpha"]):
+            t.record_stream(main)  # allocated on the side stream, read by the compose kernel on this one
+        return face, mouth
+
+
 def synthesize_sequence(views, render_face, render_mouth, dilate=False, rank=0, world=1, ring_depth=8,
-                        sink=None):
+                        sink=None, overlap=False):
     """The loop of `render_set` (synthesize_fuse.py:53-78) for this rank's frames.
 
     views: the sequence's cameras; render_face(view) / render_mouth(view) -> dicts with "render"
     [3,H,W] and "alpha" [1,H,W] (what render_motion / render_motion_mouth_con return);
     `view.background` is used when the view has one.  Frames idx = rank, rank+world, ... are
     rendered; each is handed to sink(idx, uint8 HWC numpy) in order, or collected and returned as
-    (indices, uint8 array [n_local,H,W,3]) when sink is None."""
+    (indices, uint8 array [n_local,H,W,3]) when sink is None.  overlap=True runs the two passes of a
+    frame on two streams (PairOverlap: only if render_mouth does not read device results of the
+    same frame's render_face)."""
     mine = shard_indices(len(views), rank, world)
-    ring, frames, got = None, [], []
+    ring, frames, got, pair = None, [], [], None
 
     def drain(block):
         for tag, fr in ring.collect(block=block):
@@ -128,7 +159,12 @@ def synthesize_sequence(views, render_face, render_mouth, dilate=False, rank=0, 
     with torch.no_grad():
         for idx in mine:
             view = views[idx]
-            face, mouth = render_face(view), render_mouth(view)
+            if overlap:
+                if pair is None:
+                    pair = PairOverlap(torch.device("cuda", torch.cuda.current_device()))
+                face, mouth = pair(render_face, render_mouth, view)
+            else:
+                face, mouth = render_face(view), render_mouth(view)
             H, W = face["render"].shape[-2:]
             if ring is None:
                 ring = FrameRing(int(H), int(W), depth=ring_depth, device=face["render"].device)

@@ -63,10 +63,11 @@ def test_frame_ring_and_sharded_sequence_return_frames_in_order():
     views = [View(i) for i in range(n)]
     face = lambda v: {"render": _t(data[v.i]["f"]), "alpha": _t(data[v.i]["fa"])}
     mouth = lambda v: {"render": _t(data[v.i]["m"]), "alpha": _t(data[v.i]["ma"])}
-    for world in (1, 2):
+    for world, overlap in ((1, False), (2, False), (2, True)):
         seen = {}
         for rank in range(world):
-            idx, frames = SY.synthesize_sequence(views, face, mouth, dilate=True, rank=rank, world=world, ring_depth=3)
+            idx, frames = SY.synthesize_sequence(views, face, mouth, dilate=True, rank=rank, world=world, ring_depth=3,
+                                                 overlap=overlap)
             assert idx == list(range(rank, n, world)) and frames.shape == (len(idx), H, W, 3)
             for i, fr in zip(idx, frames):
                 seen[i] = fr
@@ -75,6 +76,35 @@ def test_frame_ring_and_sharded_sequence_return_frames_in_order():
             d = data[i]
             want, _ = A.compose_frame(d["f"], d["fa"], d["m"], d["ma"], np.full((3, H, W), float(i * 10 % 256), np.float32), 13)
             assert np.array_equal(seen[i], want), i
+
+
+def test_two_stream_frame_equals_serial_frame():
+    """PairOverlap: the mouth rasterization on a side stream under the face one (separate library
+    scratch per stream) gives the frames of the serial loop, bit for bit."""
+    import torch
+    from diff_gauss import GaussianRasterizer
+    from instag_b200 import synthesis as SY
+    clouds = [U.to_torch(U.make_scene(P=6000, W=96, H=96, sh_degree=1, M=4, scale_mult=2.0, seed=s)) for s in (41, 42)]
+
+    class View:
+        def __init__(self, i):
+            self.i = i
+
+    def renderer(t):
+        def fn(view):
+            m = t["means3D"] + 0.002 * view.i
+            out = GaussianRasterizer(U.settings_from(t))(
+                means3D=m, means2D=torch.zeros_like(m), shs=t["shs"], opacities=t["opacities"], scales=t["scales"],
+                rotations=t["rotations"], extra_attrs=t.get("extra_attrs"))
+            return {"render": out[0], "alpha": out[3]}
+        return fn
+
+    views = [View(i) for i in range(12)]
+    face, mouth = renderer(clouds[0]), renderer(clouds[1])
+    i0, serial = SY.synthesize_sequence(views, face, mouth, ring_depth=4)
+    i1, both = SY.synthesize_sequence(views, face, mouth, ring_depth=4, overlap=True)
+    assert i0 == i1 == list(range(12)) and serial.any()
+    assert np.array_equal(serial, both)
 
 
 def test_activate_matches_golden_forward_and_backward():

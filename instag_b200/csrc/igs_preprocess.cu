@@ -104,6 +104,7 @@ __global__ void __launch_bounds__(PRE_THREADS, 2) preprocess_kernel(PreArgs a) {
   const int T = a.grid_x * a.grid_y;
   if (HIST_SMEM)
     for (int t = tid; t < T; t += PRE_THREADS) s_hist[t] = 0u;
+  pdl_wait(); // launched as a programmatic dependent of whatever precedes it on the stream
   if (tid < 16) { s_view[tid] = __ldg(a.viewmatrix + tid); s_proj[tid] = __ldg(a.projmatrix + tid); }
   if (tid < 3) s_cam[tid] = __ldg(a.campos + tid);
   PRE_MARK(0);
@@ -371,11 +372,11 @@ void launch_preprocess(const PreArgs& a, cudaStream_t s) {
   const int T = a.grid_x * a.grid_y;
   const size_t hist = (size_t)T * sizeof(uint32_t);
   if (T <= HIST_SMEM_MAX_TILES) {
-    if (a.shs) preprocess_kernel<true, true><<<blocks, PRE_THREADS, hist, s>>>(a);
-    else preprocess_kernel<false, true><<<blocks, PRE_THREADS, hist, s>>>(a);
+    if (a.shs) launch_after(preprocess_kernel<true, true>, dim3(blocks), dim3(PRE_THREADS), hist, s, a);
+    else launch_after(preprocess_kernel<false, true>, dim3(blocks), dim3(PRE_THREADS), hist, s, a);
   } else { // images beyond ~1700x1700: count straight into global memory
-    if (a.shs) preprocess_kernel<true, false><<<blocks, PRE_THREADS, 0, s>>>(a);
-    else preprocess_kernel<false, false><<<blocks, PRE_THREADS, 0, s>>>(a);
+    if (a.shs) launch_after(preprocess_kernel<true, false>, dim3(blocks), dim3(PRE_THREADS), 0, s, a);
+    else launch_after(preprocess_kernel<false, false>, dim3(blocks), dim3(PRE_THREADS), 0, s, a);
   }
   count_launch();
 }

@@ -16,6 +16,7 @@
 #include <c10/cuda/CUDAStream.h>
 
 #include <array>
+#include <atomic>
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -102,7 +103,7 @@ GradLayout gradient_layout(int64_t P, int64_t M, int64_t ED) {
 // multicast memory): a Python callable fn(n_floats, device) -> flat float32 tensor.
 py::object* g_grad_alloc = new py::object();  // leaked on purpose (no Python at static destruction)
 std::mutex g_grad_alloc_mutex;
-bool g_have_grad_alloc = false;
+std::atomic<bool> g_have_grad_alloc{false};
 
 struct RasterizeFn : public torch::autograd::Function<RasterizeFn> {
   static variable_list forward(AutogradContext* ctx, const Tensor& means3D, const Tensor& means2D, const Tensor& sh,

@@ -83,7 +83,9 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
   // in column p ^ ((s & 1) << 4) so that both the scalar stores and the 16-byte fragment loads are
   // bank-conflict free
   __shared__ __align__(16) float s_wg[BW][2][PEND][32];
-  __shared__ float4 s_pend[BW][PEND]; // {mean.x, mean.y, gaussian id bits, -}
+  // 512-byte stride per warp (PEND = 16 records used): the fill level of a warp's queue is then
+  // (address & 511) >> 4, with no base address to keep in (or recompute into) a register
+  __shared__ __align__(512) float4 s_pend[BW][32]; // {mean.x, mean.y, gaussian id bits, -}
   // right-hand fragments, one float4 per lane: [0..1] dL_dpixel TF32 hi, [2..3] lo (per unit),
   // and the moment basis (the same for every warp and unit)
   __shared__ float4 s_bf[BW][4][32];
@@ -356,14 +358,14 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
       const bool anya = __any_sync(0xffffffffu, va), anyb = __any_sync(0xffffffffu, vb);
       if (anya) blend(j0, a1, Ga, ala, va);
       if (anyb) blend(j1, b1, Gb, alb, vb);
-      if (pend_at >= spend + (PEND - 1) * 16) { // the next trip may park two more
-        flush((int)(pend_at - spend) >> 4);
+      if ((pend_at & 511u) >= (PEND - 1) * 16) { // the next trip may park two more
+        flush((int)(pend_at & 511u) >> 4);
         park_at = swg + lane * 4;
-        pend_at = spend;
+        pend_at &= ~511u;
       }
     }
   }
-  if (pend_at != spend) flush((int)(pend_at - spend) >> 4);
+  if (pend_at & 511u) flush((int)(pend_at & 511u) >> 4);
   __syncwarp(); // the next unit reuses this warp's shared-memory slots
  } // unit loop
 }

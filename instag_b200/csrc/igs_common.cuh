@@ -4,6 +4,7 @@
 #include <cstdint>
 #include <cstddef>
 #include <cstdio>
+#include <cstdlib>
 #include <cuda_runtime.h>
 #include "../../include/igs_raster.h"
 
@@ -153,10 +154,12 @@ inline cudaError_t launch_after(void (*kernel)(KArgs...), dim3 grid, dim3 block,
                                 Args&&... args) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  // IGS_NO_PDL=1: plain stream order (griddepcontrol.wait is then a no-op); for debugging only
+  static const bool pdl = !(getenv("IGS_NO_PDL") && getenv("IGS_NO_PDL")[0] == '1');
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   at[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = at; cfg.numAttrs = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 #endif

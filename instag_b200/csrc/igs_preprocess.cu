@@ -93,7 +93,7 @@ __device__ __forceinline__ unsigned long long pre_timer() {
 #endif
 
 template <bool USE_SH, bool HIST_SMEM>
-__global__ void __launch_bounds__(PRE_THREADS, 2) preprocess_kernel(PreArgs a) {
+__global__ void __launch_bounds__(PRE_THREADS, 1024 / PRE_THREADS) preprocess_kernel(PreArgs a) {
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   __shared__ uint32_t s_warp_sum[PRE_THREADS / 32];
   __shared__ uint32_t s_last;

@@ -221,10 +221,9 @@ struct RasterizeFn : public torch::autograd::Function<RasterizeFn> {
         flat = (*g_grad_alloc)(lay.total, py::cast(dev)).cast<Tensor>();
     }
     if (!flat.defined()) flat = at::empty({lay.total}, f32);
-    std::array<Tensor, 10> g;
-    for (int i = 0; i < 10; ++i) g[i] = flat.narrow(0, lay.start[i], P * lay.width[i]).view({P, lay.width[i]});
-    g[6] = g[6].view({P, M, 3});
-    if (ED == 0) g[9] = at::empty(extra_attrs.sizes(), f32);  // no elements; the shape autograd expects
+    // the kernel writes all ten blocks; tensor views are only made for the gradients autograd wants
+    float* const base = lay.total ? flat.data_ptr<float>() : nullptr;
+    auto gptr = [&](int i) -> float* { return (base && P * lay.width[i]) ? base + lay.start[i] : nullptr; };
     Tensor& accum = sc.buf(sc.accum, sc.accum_dirty, igs_accum_bytes((int32_t)P, (int32_t)ED), dev, true);
 
     auto grad = [&](const Tensor& t, int64_t C) { return t.defined() ? f32c(t) : sc.zero_img(C, H, W, dev); };
@@ -255,10 +254,10 @@ struct RasterizeFn : public torch::autograd::Function<RasterizeFn> {
     a.accum = accum.data_ptr();
     a.accum_clean = 1;
     sc.accum_dirty = true;
-    a.dL_dmeans2D = fptr_mut(g[0]), a.dL_dcolors = fptr_mut(g[1]), a.dL_dopacity = fptr_mut(g[2]);
-    a.dL_dmeans3D = fptr_mut(g[3]), a.dL_dcov3D = fptr_mut(g[4]), a.dL_dnorm3D = fptr_mut(g[5]);
-    a.dL_dsh = fptr_mut(g[6]), a.dL_dscales = fptr_mut(g[7]), a.dL_drotations = fptr_mut(g[8]);
-    a.dL_dextra_attrs = fptr_mut(g[9]);
+    a.dL_dmeans2D = gptr(0), a.dL_dcolors = gptr(1), a.dL_dopacity = gptr(2);
+    a.dL_dmeans3D = gptr(3), a.dL_dcov3D = gptr(4), a.dL_dnorm3D = gptr(5);
+    a.dL_dsh = gptr(6), a.dL_dscales = gptr(7), a.dL_drotations = gptr(8);
+    a.dL_dextra_attrs = gptr(9);
     int st = igs_backward(&a, stream);
     if (st != IGS_OK) fail(st, "backward");
     sc.accum_dirty = false;
@@ -268,8 +267,13 @@ struct RasterizeFn : public torch::autograd::Function<RasterizeFn> {
     // those of the empty 'None' sentinels) are dropped, as autograd does with the reference's.
     static const int src[10] = {3, 0, 6, 1, 2, 7, 8, 4, 5, 9};
     variable_list out(22);
-    for (int i = 0; i < 10; ++i)
-      if (ctx->needs_input_grad(i)) out[i] = g[src[i]];
+    for (int i = 0; i < 10; ++i) {
+      if (!ctx->needs_input_grad(i)) continue;
+      const int k = src[i];
+      if (k == 9 && ED == 0) out[i] = at::empty(extra_attrs.sizes(), f32);  // no elements; the shape autograd expects
+      else if (k == 6) out[i] = flat.as_strided({P, M, 3}, {3 * M, 3, 1}, lay.start[k]);
+      else out[i] = flat.as_strided({P, lay.width[k]}, {lay.width[k], 1}, lay.start[k]);
+    }
     return out;
   }
 };

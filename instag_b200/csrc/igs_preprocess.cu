@@ -276,19 +276,23 @@ __global__ void __launch_bounds__(PRE_THREADS, 1024 / PRE_THREADS) preprocess_ke
       if (w < warp) run += s_warp_sum[w];
       all += s_warp_sum[w];
     }
-    for (int b = b0; b < b1; b++) {
-      a.block_prefix[b] = run;
-      run += __ldcg(a.block_total + b);
+    if (bper == 1) { // P <= PRE_THREADS^2: this thread's one total is already in a register
+      if (b0 < b1) a.block_prefix[b0] = run;
+    } else {
+      for (int b = b0; b < b1; b++) {
+        a.block_prefix[b] = run;
+        run += __ldcg(a.block_total + b);
+      }
     }
     if (tid == 0) {
       a.header->num_rendered = all;
       a.header->overflow = (int64_t)all > a.capacity ? 1u : 0u;
       // straight into the caller's pinned host slot: a 4-byte copy-engine transfer between two
       // kernels costs ~12 us of stream time on B200, a posted store costs nothing
-      if (a.num_rendered_host) {
-        *(volatile int32_t*)a.num_rendered_host = (int32_t)all;
-        __threadfence_system(); // the host polls this slot
-      }
+      // No system-scope fence after it: the store is posted to the host at once, while a
+      // __threadfence_system() here held the whole CTA at its next barrier for the PCIe round trip
+      // (3-4 us of every frame, measured with IGS_PRE_TRACE); the host polls this slot.
+      if (a.num_rendered_host) *(volatile int32_t*)a.num_rendered_host = (int32_t)all;
     }
   }
   // (3) tile counts -> ranges and cursors

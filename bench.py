@@ -35,7 +35,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="igs", choices=["igs", "reference"])
-    ap.add_argument("--workload", default="C2", choices=["C2", "C3_face", "C3_mouth", "C1", "C5"])
+    ap.add_argument("--workload", default="C2", choices=["C2", "C3", "C3_face", "C3_mouth", "C1", "C5"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-synth", action="store_true", help="skip the auxiliary forward-only synthesis fps")
@@ -298,6 +298,8 @@ def main():
         return  # the reference arm is a single-GPU number: rank 0 alone runs it
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
+    if a.workload == "C3":  # a single-camera step: replicas only, rank 0 reports it
+        return c3_pair(a, torch, dist, device, local) if rank == 0 else None
     if world > 1 and a.impl == "igs":
         dist.init_process_group("nccl", device_id=device)
     eff_world = world if a.impl == "igs" else 1
@@ -406,6 +408,57 @@ def main():
     if world > 1 and a.impl == "igs":
         dist.barrier()
         dist.destroy_process_group()
+
+
+def c3_pair(a, torch, dist, device, local):
+    """BASELINE config 3, the train_fuse_con step: two rasterizations per frame, the mouth cloud
+    (30k Gaussians) then the face cloud (100k), SH degree 1, both forward + backward.
+    One JSON line: frames/s of the pair, device-resident and end to end, either arm."""
+    from instag_b200 import synthetic as S
+    arms = []
+    for name, seed in (("C3_mouth", 1), ("C3_face", 0)):
+        cfg = dict(S.CONFIGS[name])
+        sc = dict(S.make_cloud(cfg["P"], sh_degree=cfg["sh_degree"], M=cfg["M"], seed=seed))
+        sc.update(S.make_camera(cfg["W"], cfg["H"]))
+        sc["bg"] = np.asarray(cfg["bg"], np.float32)
+        arms.append(Arm(a.impl, sc, S.upstream_grads(cfg["H"], cfg["W"], extra_dims=1, seed=1), device))
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=device)
+
+    def step():
+        for arm in arms:
+            arm.step_raw()
+
+    def step_e2e():
+        for arm in arms:
+            arm.step_e2e()
+
+    sampler = ClockSampler(local)
+    step()
+    torch.cuda.synchronize()
+    sampler.start()
+    ms, per, wall = timed(torch, dist, step, a.steps, a.warmup, flush, 1)
+    ms_e2e, _, _ = timed(torch, dist, step_e2e, a.steps, max(a.warmup, 3), flush, 1)
+    clocks = sampler.result()
+    launches = 0
+    if a.impl == "igs":
+        from instag_b200 import _native as NV
+        l0 = NV.launch_count()
+        step()
+        torch.cuda.synchronize()
+        launches = NV.launch_count() - l0
+    p10, p50, p90 = (float(np.percentile(per, q)) for q in (10, 50, 90))
+    print(json.dumps({
+        "metric": "fused face+mouth step: two rasterizations fwd+bwd per frame, frames/sec @512^2", "value": 1000.0 / ms,
+        "unit": "frames/s", "n_gpus": 1, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "impl": a.impl,
+        "config": {"workload": "C3: mouth P=30000 then face P=100000 Gaussians, SH deg 1 M=4, 512x512, ED=1, "
+                               "forward+backward each", "num_rendered": [int(arm.last[0]) for arm in arms],
+                   "l2": "flushed between steps (256 MiB memset outside the per-step event pairs)"},
+        "e2e": {"value": 1000.0 / ms_e2e, "unit": "frames/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": sum(arm.h2d_bytes for arm in arms), "d2h_bytes_per_step": 8},
+        "clocks": clocks, "wall_s_timed_region": wall, "ms_per_step_p10_p50_p90": [p10, p50, p90],
+        "gpu_launches": launches * a.steps, "gpu_launches_per_step": launches}))
 
 
 def load_peaks():

@@ -108,3 +108,27 @@ def test_against_golden(path):
     g = S.upstream_grads(sc["H"], sc["W"], extra_dims=kw.get("ED", 1), seed=11)
     ours = U.run_igs(sc, grads=g)
     _check_against(ours, gold, sc, exact_geom=True, floor=float(gold["spread"].max()))
+
+
+# ---- BASELINE.json's configurations at full size --------------------------------------------
+# The same clouds and camera bench.py times (instag_b200/synthetic.py CONFIGS), held against the
+# unmodified reference CUDA rasterizer at the same bar as the small scenes: every integer array
+# bit-exact (radii, tiles_touched, offsets, 64-bit keys, point_list, ranges, n_contrib), images
+# max-abs <= 1e-5, gradients <= 1e-4 relative (floor: the reference's own run-to-run spread).
+@pytest.mark.parametrize("name", ["C1", "C2", "C3_mouth", "C3_face", "C5"])
+def test_baseline_configs_full_size_against_reference_cuda(name):
+    _need_ref()
+    cfg, cloud, cam = S.make_config(name)
+    sc = dict(cloud)
+    sc.update(cam)
+    sc["bg"] = np.asarray(cfg["bg"], np.float32)
+    g = S.upstream_grads(cfg["H"], cfg["W"], extra_dims=1, seed=1) if cfg["backward"] else None
+    ref = U.run_ref(sc, grads=g)
+    floor = 0.0
+    if g is not None:
+        ref2 = U.run_ref(sc, grads=g)
+        floor = max(U.rel_err(ref[k], ref2[k]) for k in U.GRAD_NAMES)
+        del ref2
+    ours = U.run_igs(sc, grads=g)
+    assert int(ours["num_rendered"]) > cfg["P"]  # the clouds fill the frame (N ~ 5P)
+    _check_against(ours, ref, sc, exact_geom=True, floor=floor)

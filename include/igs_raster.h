@@ -99,6 +99,14 @@ typedef struct IgsFwdArgs {
    * back to zero when they are done with it) -- so the library skips its memset of [ctrl] (one
    * stream operation less per frame) */
   int32_t ctrl_clean;
+  /* != 0 (and the slot is device-mapped pinned memory): igs_forward queues the whole frame and
+   * returns IGS_OK at once with *num_rendered = -1, without waiting for the count.  The library
+   * sets the slot to -1 before it launches; the caller reads it once the frame is known to have
+   * run, and compares it with `capacity` itself: a count above capacity means
+   * the frame's images are incomplete and it must be rendered again with larger bin / sort
+   * workspaces.  Nothing is written out of bounds in that case.  For forward-only pipelines that
+   * own the point where a frame is consumed (the synthesis driver). */
+  int32_t defer_count;
 } IgsFwdArgs;
 
 typedef struct IgsBwdArgs {

@@ -31,6 +31,7 @@ class IgsFwdArgs(C.Structure):
         ("capacity", C.c_int64),
         ("num_rendered_pinned", _p),
         ("ctrl_clean", C.c_int32),
+        ("defer_count", C.c_int32),
     ]
 
 

@@ -258,6 +258,12 @@ int igs_forward(const IgsFwdArgs* a, igs_stream_t stream, int64_t* num_rendered)
   }
   // speculative second half: sized by capacity, bounded on the device by num_rendered
   if (int r = run_bin_render(a, s)) return r;
+  if (a->defer_count && pa.num_rendered_host) {
+    // the caller reads the posted count later (slot == -1: not there yet) and holds it against
+    // the capacity itself; everything is queued, nothing on the device depends on the host
+    if (num_rendered) *num_rendered = -1;
+    return IGS_OK;
+  }
   if (!pa.num_rendered_host) {
     if (int r = check_cuda(cudaEventSynchronize(ev), "wait num_rendered")) return r;
   } else {

@@ -17,6 +17,7 @@
 
 #include <array>
 #include <atomic>
+#include <deque>
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -36,6 +37,7 @@ struct Scratch {
   std::tuple<int64_t, int64_t, int64_t> ctrl_key{-1, -1, -1};
   std::map<std::tuple<int64_t, int64_t, int64_t>, int64_t> capacity_hint;
   std::map<std::tuple<int64_t, int64_t, int64_t>, Tensor> zero_imgs;
+  int defer_next = 1, defer_in_use = 0;  // ring of count slots for calls that do not wait (see Pending)
 
   // `ctrl` and `accum` are handed to the library zeroed and come back clean from every successful
   // call; a failed call marks them dirty and they are cleared before the next one.
@@ -60,13 +62,34 @@ struct Scratch {
   }
 };
 
+// Slot 0 of `pinned` receives the count of a call that waits for it; slots 1.. are handed out in
+// turn to calls that do not (deferred counts, below).
+constexpr int kDeferSlots = 255;
+
 Scratch& scratch(int device, cudaStream_t stream) {
   // never destroyed: the tensors must not outlive the CUDA context at thread / process exit
   thread_local auto* all = new std::map<std::pair<int, cudaStream_t>, Scratch>();
   Scratch& s = (*all)[{device, stream}];
-  if (!s.pinned.defined()) s.pinned = at::zeros({4}, at::kInt).pin_memory();
+  if (!s.pinned.defined()) s.pinned = at::zeros({1 + kDeferSlots}, at::kInt).pin_memory();
   return s;
 }
+
+// ---- deferred counts (forward-only pipelines; synthesis.DeferredCounts is the Python face) ----
+// A forward call normally waits for the preprocess kernel to post num_rendered, because only then
+// is it known that the instance workspaces were large enough.  A pipeline that renders frame after
+// frame without gradients and owns the point where a frame is consumed can take that wait off the
+// host's critical path: the call queues the frame, notes (slot, capacity) here and returns; the
+// pipeline asks `deferred_overflowed(first, last)` when it harvests the frame -- by then the count
+// has long been posted -- and renders the frame again if it was cut short.
+struct Pending {
+  volatile int32_t* slot;
+  int64_t capacity;
+  int64_t* hint;  // the scratch's capacity hint for this (P, H, W): raised from the count when it is read
+  Scratch* owner; // its ring of slots gets this one back
+};
+thread_local bool t_defer = false;
+thread_local int64_t t_serial = 0;                              // deferred calls so far on this thread
+thread_local std::deque<std::pair<int64_t, Pending>>* t_pending = nullptr;  // (serial, entry), oldest first
 
 inline Tensor f32c(const Tensor& t) {
   Tensor r = t.scalar_type() == at::kFloat ? t : t.to(at::kFloat);
@@ -168,6 +191,30 @@ struct RasterizeFn : public torch::autograd::Function<RasterizeFn> {
     a.num_rendered_pinned = sc.pinned.data_ptr<int32_t>();
     a.ctrl_clean = 1;
     sc.ctrl_dirty = true;  // until the call has returned without an error
+
+    // no graph is being recorded, the sizes have been seen before, a slot is free: do not wait for the count
+    const bool defer = t_defer && P > 0 && hint != sc.capacity_hint.end() && sc.defer_in_use < kDeferSlots &&
+                       !(at::GradMode::is_enabled() &&
+                         (means3D.requires_grad() || sh.requires_grad() || colors_precomp.requires_grad() ||
+                          opacities.requires_grad() || scales.requires_grad() || rotations.requires_grad() ||
+                          cov3Ds_precomp.requires_grad() || norm3Ds_precomp.requires_grad() ||
+                          extra_attrs.requires_grad() || means2D.requires_grad()));
+    if (defer) {
+      const int slot = sc.defer_next;
+      sc.defer_next = slot % kDeferSlots + 1;
+      sc.defer_in_use++;
+      a.num_rendered_pinned = sc.pinned.data_ptr<int32_t>() + slot;
+      a.defer_count = 1;
+      const int st = igs_forward(&a, stream, nullptr);
+      if (st != IGS_OK && st != IGS_ERR_CAPACITY) {  // (a count already known to be too large is found at harvest)
+        sc.defer_in_use--;
+        fail(st, "forward");
+      }
+      sc.ctrl_dirty = false;
+      if (!t_pending) t_pending = new std::deque<std::pair<int64_t, Pending>>();
+      t_pending->push_back({t_serial++, Pending{a.num_rendered_pinned, capacity, &hint->second, &sc}});
+      return {color, depth, norm, alpha, radii, extra};
+    }
 
     int64_t num_rendered = 0;
     int st = igs_forward(&a, stream, &num_rendered);
@@ -289,6 +336,37 @@ std::vector<Tensor> rasterize(const Tensor& means3D, const Tensor& means2D, cons
                             scale_modifier, H, W, sh_degree, prefiltered, fuse_normalize);
 }
 
+bool set_deferred_counts(bool on) {
+  const bool was = t_defer;
+  t_defer = on;
+  return was;
+}
+int64_t deferred_mark() { return t_serial; }
+
+// Reads the counts of the deferred calls with serial in [.., last) that have not been read yet
+// (waiting for any that has not been posted: the caller asks after the frame has been consumed,
+// so there is normally nothing to wait for) and tells whether one with serial >= first exceeded
+// its capacity.  Raises the capacity hints from the counts, as a waiting call would have.
+bool deferred_overflowed(int64_t first, int64_t last) {
+  bool over = false;
+  while (t_pending && !t_pending->empty() && t_pending->front().first < last) {
+    const int64_t serial = t_pending->front().first;
+    const Pending p = t_pending->front().second;
+    t_pending->pop_front();
+    for (uint64_t spin = 1; *p.slot == -1; ++spin) {
+      TORCH_CHECK(spin < (1ull << 33), "libigs_raster: a deferred num_rendered was never posted");
+#if defined(__x86_64__) || defined(__i386__)
+      __builtin_ia32_pause();
+#endif
+    }
+    const int64_t n = (int64_t)(uint32_t)*p.slot;
+    p.owner->defer_in_use--;
+    *p.hint = std::max<int64_t>(*p.hint, (int64_t)(n * 1.25) + 4096);
+    if (serial >= first && n > p.capacity) over = true;
+  }
+  return over;
+}
+
 void set_gradient_allocator(py::object fn) {
   std::lock_guard<std::mutex> lock(g_grad_alloc_mutex);
   g_have_grad_alloc = !fn.is_none();
@@ -302,5 +380,10 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("rasterize", &rasterize, py::call_guard<py::gil_scoped_release>(),
         "forward of the rasterizer as one autograd node: (color, depth, norm, alpha, radii, extra)");
   m.def("set_gradient_allocator", &set_gradient_allocator, "fn(n_floats, device) -> flat float32 tensor, or None");
+  m.def("set_deferred_counts", &set_deferred_counts,
+        "this thread's forward-only calls stop waiting for num_rendered (True) or wait again (False); returns the old setting");
+  m.def("deferred_mark", &deferred_mark, "serial number the next deferred call of this thread will get");
+  m.def("deferred_overflowed", &deferred_overflowed, py::call_guard<py::gil_scoped_release>(),
+        "reads the counts of the deferred calls before serial `last`; True if one at or after `first` exceeded its capacity");
   m.def("library_version", []() { return std::string(igs_version()); });
 }

@@ -16,6 +16,8 @@ functions (which call `diff_gauss`, i.e. this library); what changes is everythi
 
 No CPU fallback: CUDA tensors only.
 """
+import contextlib
+
 import numpy as np
 import torch
 
@@ -134,8 +136,58 @@ class PairOverlap:
         return face, mouth
 
 
+class DeferredCounts:
+    """Takes the wait for `num_rendered` off the host's critical path of a forward-only pipeline.
+
+    A rasterizer call normally returns only after the per-Gaussian kernel has posted the number of
+    (tile, Gaussian) instances, because only then is it known that the instance workspaces (sized
+    from the previous frame's count + 25 %) were large enough; the host therefore meets the GPU
+    once per call and cannot queue ahead.  Inside `with DeferredCounts() as dc:` the no-grad calls
+    of this thread (compiled host side only) queue their frame and return at once.  The pipeline
+    brackets the calls of a frame with `tok = dc.begin()` ... `dc.end(tok)` and asks
+    `dc.cut_short(tok)` when it consumes the frame (after its device->host copy has finished, so
+    the counts are there): True means an instance list did not fit and the frame must be rendered
+    again -- `with dc.waiting():` restores the ordinary behaviour (which also grows the
+    workspaces) for that.  Frames must be asked about in the order they were rendered."""
+
+    def __init__(self):
+        from . import rasterizer as R
+        self.b = R.binding() if R.host_path() == "cxx" else None
+        self.was = False
+
+    def __enter__(self):
+        if self.b is not None:
+            self.was = self.b.set_deferred_counts(True)
+        return self
+
+    def __exit__(self, *exc):
+        if self.b is not None:
+            self.b.deferred_overflowed(0, self.b.deferred_mark())  # read what is outstanding: the slots come back
+            self.b.set_deferred_counts(self.was)
+        return False
+
+    def begin(self):
+        return [self.b.deferred_mark() if self.b is not None else 0, None]
+
+    def end(self, tok):
+        tok[1] = self.b.deferred_mark() if self.b is not None else 0
+        return tok
+
+    def cut_short(self, tok):
+        return self.b is not None and tok[1] > tok[0] and bool(self.b.deferred_overflowed(tok[0], tok[1]))
+
+    @contextlib.contextmanager
+    def waiting(self):
+        was = self.b.set_deferred_counts(False) if self.b is not None else False
+        try:
+            yield
+        finally:
+            if self.b is not None:
+                self.b.set_deferred_counts(was)
+
+
 def synthesize_sequence(views, render_face, render_mouth, dilate=False, rank=0, world=1, ring_depth=8,
-                        sink=None, overlap=False):
+                        sink=None, overlap=False, deferred_counts=True):
     """The loop of `render_set` (synthesize_fuse.py:53-78) for this rank's frames.
 
     views: the sequence's cameras; render_face(view) / render_mouth(view) -> dicts with "render"
@@ -144,27 +196,45 @@ def synthesize_sequence(views, render_face, render_mouth, dilate=False, rank=0, 
     rendered; each is handed to sink(idx, uint8 HWC numpy) in order, or collected and returned as
     (indices, uint8 array [n_local,H,W,3]) when sink is None.  overlap=True runs the two passes of a
     frame on two streams (PairOverlap: only if render_mouth does not read device results of the
-    same frame's render_face)."""
+    same frame's render_face).  deferred_counts=True: the rasterizer calls do not wait for their
+    instance counts (DeferredCounts); a frame whose count turns out to have exceeded the workspaces
+    is rendered again before it is handed on."""
     mine = shard_indices(len(views), rank, world)
     ring, frames, got, pair = None, [], [], None
+    toks = {}
+    dc = DeferredCounts()
+
+    def render_pair(view):
+        nonlocal pair
+        if overlap:
+            if pair is None:
+                pair = PairOverlap(torch.device("cuda", torch.cuda.current_device()))
+            return pair(render_face, render_mouth, view)
+        return render_face(view), render_mouth(view)
+
+    def again(idx):
+        # the ordinary, waiting calls (they grow the workspaces), composed and fetched synchronously
+        with dc.waiting():
+            face, mouth = render_pair(views[idx])
+            return compose_frame(face["render"], face["alpha"], mouth["render"], mouth["alpha"],
+                                 getattr(views[idx], "background", None), dilate=dilate).cpu().numpy()
 
     def drain(block):
         for tag, fr in ring.collect(block=block):
+            if dc.cut_short(toks.pop(tag)):
+                fr = again(tag)
             if sink is not None:
                 sink(tag, fr)
             else:
                 got.append(tag)
                 frames.append(fr)
 
-    with torch.no_grad():
+    with torch.no_grad(), (dc if deferred_counts else contextlib.nullcontext()):
         for idx in mine:
             view = views[idx]
-            if overlap:
-                if pair is None:
-                    pair = PairOverlap(torch.device("cuda", torch.cuda.current_device()))
-                face, mouth = pair(render_face, render_mouth, view)
-            else:
-                face, mouth = render_face(view), render_mouth(view)
+            tok = dc.begin()
+            face, mouth = render_pair(view)
+            toks[idx] = dc.end(tok)
             H, W = face["render"].shape[-2:]
             if ring is None:
                 ring = FrameRing(int(H), int(W), depth=ring_depth, device=face["render"].device)
@@ -174,8 +244,8 @@ def synthesize_sequence(views, render_face, render_mouth, dilate=False, rank=0, 
                           getattr(view, "background", None), dilate=dilate, out=ring.slot())
             ring.commit(idx)
             drain(block=False)
-    if ring is not None:
-        drain(block=True)
+        if ring is not None:
+            drain(block=True)
     if sink is not None:
         return mine, None
     return got, (np.stack(frames) if frames else np.zeros((0, 0, 0, 3), np.uint8))

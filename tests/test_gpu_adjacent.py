@@ -254,3 +254,73 @@ def _torch_ssim(img1, img2):
     s12 = F.conv2d(img1 * img2, w, padding=5, groups=C_) - mu1 * mu2
     C1, C2 = 0.01 ** 2, 0.03 ** 2
     return (((2 * mu1 * mu2 + C1) * (2 * s12 + C2)) / ((mu1.pow(2) + mu2.pow(2) + C1) * (s1 + s2 + C2))).mean()
+
+
+def test_deferred_counts_give_the_same_frames_and_repair_a_frame_that_was_cut_short():
+    """DeferredCounts: the no-grad calls of the sequence do not wait for num_rendered.  The splats
+    grow 3x in the middle of the sequence, so the instance count of that frame exceeds the
+    workspaces sized from the frame before (+25 %): the driver must notice when it harvests the
+    frame and render it again.  Frames equal those of the waiting loop bit for bit."""
+    import torch
+    from diff_gauss import GaussianRasterizer
+    from instag_b200 import rasterizer as R
+    from instag_b200 import synthesis as SY
+    if R.host_path() != "cxx":
+        pytest.skip("deferred counts live in the compiled host side")
+    clouds = [U.to_torch(U.make_scene(P=6000, W=96, H=96, sh_degree=1, M=4, scale_mult=1.0, seed=s)) for s in (51, 52)]
+
+    class View:
+        def __init__(self, i):
+            self.i = i
+
+    def renderer(t):
+        def fn(view):
+            m = t["means3D"] + 0.002 * view.i
+            sc = t["scales"] * (3.0 if 5 <= view.i < 9 else 1.0)
+            out = GaussianRasterizer(U.settings_from(t))(
+                means3D=m, means2D=torch.zeros_like(m), shs=t["shs"], opacities=t["opacities"], scales=sc,
+                rotations=t["rotations"], extra_attrs=t.get("extra_attrs"))
+            return {"render": out[0], "alpha": out[3]}
+        return fn
+
+    views = [View(i) for i in range(14)]
+    face, mouth = renderer(clouds[0]), renderer(clouds[1])
+    b = R.binding()
+    again = []
+    real = b.deferred_overflowed
+
+    s0 = b.deferred_mark()
+    i0, waiting = SY.synthesize_sequence(views, face, mouth, ring_depth=4, deferred_counts=False)
+    assert b.deferred_mark() == s0  # nothing deferred by the waiting loop
+
+    class Spy:  # the binding with deferred_overflowed watched
+        def __getattr__(self, k):
+            return getattr(b, k)
+
+        def deferred_overflowed(self, first, last):
+            r = real(first, last)
+            again.append(bool(r))
+            return r
+
+    dc_init = SY.DeferredCounts.__init__
+
+    def spy_init(self):
+        dc_init(self)
+        self.b = Spy()
+    SY.DeferredCounts.__init__ = spy_init
+    try:
+        for overlap in (False, True):
+            again.clear()
+            s0 = b.deferred_mark()
+            i1, deferred = SY.synthesize_sequence(views, face, mouth, ring_depth=4, overlap=overlap)
+            assert i0 == i1 == list(range(14))
+            assert b.deferred_mark() - s0 >= 2 * 12  # all but the first calls of each cloud (and the repairs) deferred
+            assert any(again), "the 3x frame should have exceeded its workspaces"
+            assert np.array_equal(waiting, deferred)
+    finally:
+        SY.DeferredCounts.__init__ = dc_init
+    # outside the context the calls wait again
+    s1 = b.deferred_mark()
+    with torch.no_grad():
+        face(views[0])
+    assert b.deferred_mark() == s1

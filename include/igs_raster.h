@@ -188,6 +188,13 @@ void igs_img_layout(int32_t W, int32_t H, int64_t* off2);
  * the caller re-runs the second half with bigger bin/sort/ctrl buffers. */
 int igs_forward(const IgsFwdArgs* args, igs_stream_t stream, int64_t* num_rendered);
 
+/* The second half of igs_forward's contract for a call made with defer_count != 0: waits until
+ * the count has been posted into args->num_rendered_pinned (same args as the igs_forward call),
+ * stores it in *num_rendered and returns IGS_OK, or IGS_ERR_CAPACITY exactly as igs_forward
+ * would have.  Lets the caller do its own bookkeeping between queueing the frame and needing
+ * the count. */
+int igs_forward_count(const IgsFwdArgs* args, igs_stream_t stream, int64_t* num_rendered);
+
 /* Second half only (duplicate, tile sort, render), after IGS_ERR_CAPACITY: same geom / img /
  * ctrl buffers as the call that overflowed, bigger bin / sort and capacity. */
 int igs_forward_bin_render(const IgsFwdArgs* args, igs_stream_t stream);

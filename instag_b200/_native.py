@@ -70,6 +70,7 @@ SYMBOLS = {
     "igs_img_layout": (None, [C.c_int32, C.c_int32, C.POINTER(C.c_int64)]),
     "igs_forward": (C.c_int, [C.POINTER(IgsFwdArgs), _p, C.POINTER(C.c_int64)]),
     "igs_forward_bin_render": (C.c_int, [C.POINTER(IgsFwdArgs), _p]),
+    "igs_forward_count": (C.c_int, [C.POINTER(IgsFwdArgs), _p, C.POINTER(C.c_int64)]),
     "igs_backward": (C.c_int, [C.POINTER(IgsBwdArgs), _p]),
     "igs_profile_enable": (C.c_int, [C.c_int]),
     "igs_profile_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_int32)]),

@@ -259,29 +259,36 @@ int igs_forward(const IgsFwdArgs* a, igs_stream_t stream, int64_t* num_rendered)
   // speculative second half: sized by capacity, bounded on the device by num_rendered
   if (int r = run_bin_render(a, s)) return r;
   if (a->defer_count && pa.num_rendered_host) {
-    // the caller reads the posted count later (slot == -1: not there yet) and holds it against
-    // the capacity itself; everything is queued, nothing on the device depends on the host
+    // the caller reads the posted count later (igs_forward_count, or the slot itself: -1 = not
+    // there yet) and holds it against the capacity; everything is queued, nothing on the device
+    // depends on the host
     if (num_rendered) *num_rendered = -1;
     return IGS_OK;
   }
   if (!pa.num_rendered_host) {
     if (int r = check_cuda(cudaEventSynchronize(ev), "wait num_rendered")) return r;
-  } else {
-    // Wait for the posted count itself, not for an event: nothing sits between the kernels on the
-    // stream, and the host wakes when the store lands (the last preprocess CTA posts it before it
-    // builds the tile ranges).  cudaStreamQuery only guards against a kernel that died without posting.
-    for (unsigned spin = 1; *slot == -1; spin++) {
-      if ((spin & 0x3ff) == 0) {
-        const cudaError_t q = cudaStreamQuery(s);
-        if (q == cudaSuccess) break; // the stream is idle; the count is there, or it never will be
-        if (q != cudaErrorNotReady) return check_cuda(q, "wait num_rendered");
-      }
-#if defined(__x86_64__) || defined(__i386__)
-      __builtin_ia32_pause();
-#endif
-    }
-    if (*slot == -1) { set_error("the preprocess kernel did not post num_rendered"); return IGS_ERR_CUDA; }
   }
+  return igs_forward_count(a, stream, num_rendered);
+}
+
+int igs_forward_count(const IgsFwdArgs* a, igs_stream_t stream, int64_t* num_rendered) {
+  if (!a || !a->num_rendered_pinned) { set_error("igs_forward_count: no slot"); return IGS_ERR_INVALID; }
+  cudaStream_t s = (cudaStream_t)stream;
+  volatile int32_t* const slot = (volatile int32_t*)a->num_rendered_pinned;
+  // Wait for the posted count itself, not for an event: nothing sits between the kernels on the
+  // stream, and the host wakes when the store lands (the last preprocess CTA posts it before it
+  // builds the tile ranges).  cudaStreamQuery only guards against a kernel that died without posting.
+  for (unsigned spin = 1; *slot == -1; spin++) {
+    if ((spin & 0x3ff) == 0) {
+      const cudaError_t q = cudaStreamQuery(s);
+      if (q == cudaSuccess) break; // the stream is idle; the count is there, or it never will be
+      if (q != cudaErrorNotReady) return check_cuda(q, "wait num_rendered");
+    }
+#if defined(__x86_64__) || defined(__i386__)
+    __builtin_ia32_pause();
+#endif
+  }
+  if (*slot == -1) { set_error("the preprocess kernel did not post num_rendered"); return IGS_ERR_CUDA; }
   const int64_t n = (int64_t)(uint32_t)*a->num_rendered_pinned;
   if (num_rendered) *num_rendered = n;
   if (n > a->capacity) {

@@ -135,3 +135,36 @@ def test_reference_error_texts():
     with pytest.raises(RuntimeError, match="CUDA-only"):
         r(means3D=t["means3D"].cpu(), means2D=m2, opacities=t["opacities"], colors_precomp=t["colors_precomp"],
           scales=t["scales"], rotations=t["rotations"])
+
+
+def test_deferred_count_through_the_c_abi():
+    """IgsFwdArgs.defer_count + igs_forward_count: the frame is queued without waiting, the count
+    (and IGS_ERR_CAPACITY, exactly as igs_forward would have returned it) comes from the second
+    call; images equal those of the waiting call."""
+    from instag_b200 import _native as N
+    from instag_b200 import rasterizer as R
+    sc = U.make_scene(P=3000, W=96, H=80, sh_degree=None, ED=1, scale_mult=2.0, seed=21)
+    t = U.to_torch(sc)
+    out = R._forward_native(*U.raw_args_fwd(t))
+    n0, color0 = int(out[0]), out[1].clone()
+    torch.cuda.synchronize()
+    dev = t["means3D"].device
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    s = R._get_scratch(dev, stream)
+    a, lib = s.fwd_args, N.lib()
+    assert n0 > 0 and a.capacity >= n0
+    out[1].zero_()
+    a.defer_count = 1
+    try:
+        assert lib.igs_forward(s.fwd_args_ref, stream, s.n_out_ref) == N.IGS_OK and s.n_out.value == -1
+        assert lib.igs_forward_count(s.fwd_args_ref, stream, s.n_out_ref) == N.IGS_OK and s.n_out.value == n0
+        torch.cuda.synchronize()
+        assert torch.equal(out[1], color0)
+        # a workspace that is too small: nothing faults, the count says so
+        a.capacity = n0 - 1
+        assert lib.igs_forward(s.fwd_args_ref, stream, s.n_out_ref) == N.IGS_OK
+        assert lib.igs_forward_count(s.fwd_args_ref, stream, s.n_out_ref) == N.IGS_ERR_CAPACITY and s.n_out.value == n0
+        torch.cuda.synchronize()
+    finally:
+        a.defer_count = 0
+        s.dirty.add("ctrl")

@@ -119,3 +119,26 @@ def test_host_path_switch(monkeypatch):
     assert R.host_path() == "cxx"
     monkeypatch.setenv("IGS_HOST", "python")
     assert R.host_path() == "python"
+
+
+def test_deferred_counts_context_without_a_gpu(monkeypatch):
+    """synthesis.DeferredCounts is inert with the Python host side, and with the compiled one it
+    only flips this thread's switch (restored on exit); no frame is outstanding, so nothing is cut short."""
+    from instag_b200 import rasterizer as R
+    from instag_b200 import synthesis as SY
+    monkeypatch.setenv("IGS_HOST", "python")
+    dc = SY.DeferredCounts()
+    with dc:
+        tok = dc.end(dc.begin())
+        assert dc.b is None and not dc.cut_short(tok)
+    monkeypatch.setenv("IGS_HOST", "cxx")
+    b = R.binding()
+    assert b.set_deferred_counts(False) is False
+    with SY.DeferredCounts() as dc:
+        assert b.set_deferred_counts(True) is True  # the context switched it on
+        tok = dc.end(dc.begin())
+        assert tok[0] == tok[1] == b.deferred_mark() and not dc.cut_short(tok)
+        with dc.waiting():
+            assert b.set_deferred_counts(False) is False
+        assert b.set_deferred_counts(True) is True  # waiting() put it back
+    assert b.set_deferred_counts(False) is False  # and the context restored the caller's setting

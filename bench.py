@@ -562,9 +562,11 @@ def cloud_from_ply(path):
                 sh_degree=g["sh_degree"])
 
 
-def synth_fps(torch, dist, world, rank, flush, device, frames=60):
+def synth_fps(torch, dist, world, rank, flush, device, total_frames=1000):
     """BASELINE config 4 shape: per frame one face (100k, SH deg 1 M=4) + one mouth (30k) forward
-    rasterization; every rank renders its own frames (different cameras), no collective."""
+    rasterization; the 1000 frames of the sequence (25 fps x 40 s) are dealt out to the ranks
+    (rank r renders frames r, r+world, ...: its own cameras), no collective."""
+    frames = max(total_frames // world, 8)
     import util as U
     from instag_b200 import synthetic as S
     from instag_b200 import rasterizer as R
@@ -631,7 +633,7 @@ def synth_fps(torch, dist, world, rank, flush, device, frames=60):
     return {"value": world * 1000.0 / ms, "unit": "frames/s", "ms_per_frame": ms, "frames_rendered_again": repaired[0],
             "workload": "face 100k + mouth 30k Gaussians (SH deg 1, M=4), 512x512, forward only (the two passes "
                         "of a frame on two streams, instance counts read when the frame is harvested) + fused compose (igs_compose_frame) into a device ring, uint8 frames copied to pinned memory on a side "
-                        "stream; frames sharded over ranks, no collective"}
+                        "stream; " + f"{frames * world} frames sharded over {world} rank(s), no collective"}
 
 
 def reference_cpu_arm(a, sc, grads, backward, cfg):

@@ -89,8 +89,7 @@ typedef struct IgsFwdArgs {
   void* img;    /* [keep]    igs_img_bytes(W,H) */
   void* bin;    /* [keep]    igs_bin_bytes(capacity) */
   void* sort;   /* [scratch] igs_sort_bytes(capacity) */
-  void* ctrl;   /* [scratch] igs_ctrl_bytes(P,W,H): scan look-back state, tile counts and cursors;
-                 * must stay untouched between igs_forward and a following igs_forward_bin_render */
+  void* ctrl;   /* [scratch] igs_ctrl_bytes(P,W,H): header, tile counts and cursors */
   int64_t capacity; /* instance capacity of bin/sort */
   /* pinned host slot the library copies num_rendered into */
   int32_t* num_rendered_pinned;
@@ -107,6 +106,11 @@ typedef struct IgsFwdArgs {
    * workspaces.  Nothing is written out of bounds in that case.  For forward-only pipelines that
    * own the point where a frame is consumed (the synthesis driver). */
   int32_t defer_count;
+  /* != 0: the sorted 64-bit keys (tile << 32 | depth bits, the reference's binningState.point_list_keys,
+   * DGR rasterizer_impl.h:47-57) are written into [bin] beside point_list.  Nothing on the path reads
+   * them (the instance lists are built by tile, not by a global key sort); tests compare them with the
+   * reference's bit for bit.  0 saves 8 bytes of HBM writes per instance. */
+  int32_t write_keys;
 } IgsFwdArgs;
 
 typedef struct IgsBwdArgs {
@@ -166,6 +170,10 @@ const char* igs_last_error(void);
 
 size_t igs_geom_bytes(int32_t P);
 size_t igs_img_bytes(int32_t W, int32_t H);
+/* byte offset, inside the img workspace, of the uint32 in which the device keeps the frame's
+ * num_rendered with the state (a caller that did not wait for the count and lost its pinned slot
+ * can still read it from there) */
+size_t igs_img_info_offset(int32_t W, int32_t H);
 size_t igs_bin_bytes(int64_t capacity);
 size_t igs_sort_bytes(int64_t capacity);
 size_t igs_ctrl_bytes(int32_t P, int32_t W, int32_t H);
@@ -174,18 +182,18 @@ size_t igs_accum_bytes(int32_t P, int32_t ED);
 /* Byte offsets of the arrays inside the workspaces (for tests / inspection).
  * geom  (4): splat records float4[P][4] = {conic.xyz,opacity | x,y,depth,extra0 |
  *            r,g,b,nx | ny,nz,-,-}, tiles_touched u32[P], point_offsets u32[P]
- *            (inclusive scan), clamped u8[P] (bit c = colour channel c clamped)
- * bin   (2): point_list u32[cap], keys u64[cap]      (sorted)
+ *            (inclusive scan; only after igs_point_offsets), clamped u8[P] (bit c = colour channel c clamped)
+ * bin   (2): point_list u32[cap], keys u64[cap]      (sorted; keys only with write_keys)
  * img   (2): ranges uint2[T], n_contrib u32[H*W]  (+ private: tile order, normal lengths) */
 void igs_geom_layout(int32_t P, int64_t* off4);
 void igs_bin_layout(int64_t capacity, int64_t* off2);
 void igs_img_layout(int32_t W, int32_t H, int64_t* off2);
 
-/* Full forward.  Launches preprocess+scan, copies num_rendered to the pinned
- * slot, speculatively launches binning/sort/render for `capacity` instances,
- * then waits for the copy only.  *num_rendered receives the instance count.
- * Returns IGS_ERR_CAPACITY if it exceeds capacity: outputs are then invalid and
- * the caller re-runs the second half with bigger bin/sort/ctrl buffers. */
+/* Full forward.  Queues the per-Gaussian kernel and, sized by `capacity`, the binning, sorting
+ * and render kernels (the count of instances is posted into the pinned slot by the device on the
+ * way), then waits for the count only.  *num_rendered receives it.
+ * Returns IGS_ERR_CAPACITY if it exceeds capacity: the outputs are then invalid (the kernels wrote
+ * nothing) and the caller calls igs_forward_bin_render with bigger bin / sort buffers. */
 int igs_forward(const IgsFwdArgs* args, igs_stream_t stream, int64_t* num_rendered);
 
 /* The second half of igs_forward's contract for a call made with defer_count != 0: waits until
@@ -195,9 +203,14 @@ int igs_forward(const IgsFwdArgs* args, igs_stream_t stream, int64_t* num_render
  * the count. */
 int igs_forward_count(const IgsFwdArgs* args, igs_stream_t stream, int64_t* num_rendered);
 
-/* Second half only (duplicate, tile sort, render), after IGS_ERR_CAPACITY: same geom / img /
- * ctrl buffers as the call that overflowed, bigger bin / sort and capacity. */
+/* After IGS_ERR_CAPACITY: same geom / img / ctrl buffers as the call that overflowed, bigger
+ * bin / sort and capacity; renders the frame again and waits for its count. */
 int igs_forward_bin_render(const IgsFwdArgs* args, igs_stream_t stream);
+
+/* The reference's point_offsets -- the inclusive prefix sum of tiles_touched
+ * (cub::DeviceScan::InclusiveSum, DGR rasterizer_impl.cu:280) -- written into the geom workspace of
+ * a finished igs_forward, on request: the path itself places instances by tile and never reads it. */
+int igs_point_offsets(int32_t P, void* geom, igs_stream_t stream);
 
 int igs_backward(const IgsBwdArgs* args, igs_stream_t stream);
 

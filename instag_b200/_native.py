@@ -32,6 +32,7 @@ class IgsFwdArgs(C.Structure):
         ("num_rendered_pinned", _p),
         ("ctrl_clean", C.c_int32),
         ("defer_count", C.c_int32),
+        ("write_keys", C.c_int32),
     ]
 
 
@@ -61,6 +62,7 @@ SYMBOLS = {
     "igs_last_error": (C.c_char_p, []),
     "igs_geom_bytes": (C.c_size_t, [C.c_int32]),
     "igs_img_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
+    "igs_img_info_offset": (C.c_size_t, [C.c_int32, C.c_int32]),
     "igs_bin_bytes": (C.c_size_t, [C.c_int64]),
     "igs_sort_bytes": (C.c_size_t, [C.c_int64]),
     "igs_ctrl_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
@@ -71,6 +73,7 @@ SYMBOLS = {
     "igs_forward": (C.c_int, [C.POINTER(IgsFwdArgs), _p, C.POINTER(C.c_int64)]),
     "igs_forward_bin_render": (C.c_int, [C.POINTER(IgsFwdArgs), _p]),
     "igs_forward_count": (C.c_int, [C.POINTER(IgsFwdArgs), _p, C.POINTER(C.c_int64)]),
+    "igs_point_offsets": (C.c_int, [C.c_int32, _p, _p]),
     "igs_backward": (C.c_int, [C.POINTER(IgsBwdArgs), _p]),
     "igs_profile_enable": (C.c_int, [C.c_int]),
     "igs_profile_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_int32)]),

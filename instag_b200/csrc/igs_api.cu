@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <initializer_list>
 #include "igs_common.cuh"
 #include "igs_kernels.cuh"
 
@@ -80,6 +81,14 @@ static int32_t* device_view_of_pinned(int32_t* host) {
   return last_dev;
 }
 
+// the kernels use 16-byte vector accesses on the caller's arrays (include/igs_raster.h: "all device
+// pointers must be 16-byte aligned"); a misaligned one would fault and poison the CUDA context
+static bool misaligned(std::initializer_list<const void*> ps) {
+  for (const void* p : ps)
+    if ((uintptr_t)p & 15u) return true;
+  return false;
+}
+
 static int validate_fwd(const IgsFwdArgs* a) {
   if (!a) { set_error("null args"); return IGS_ERR_INVALID; }
   if (a->P < 0 || a->W <= 0 || a->H <= 0) { set_error("bad sizes P=%d W=%d H=%d", a->P, a->W, a->H); return IGS_ERR_INVALID; }
@@ -101,6 +110,11 @@ static int validate_fwd(const IgsFwdArgs* a) {
     set_error("null workspace"); return IGS_ERR_INVALID;
   }
   if (a->capacity >= (1ll << 30)) { set_error("capacity must be < 2^30 instances"); return IGS_ERR_INVALID; }
+  if (misaligned({a->means3D, a->shs, a->colors_precomp, a->opacities, a->scales, a->rotations, a->cov3Ds_precomp,
+                  a->norm3Ds_precomp, a->extra_attrs, a->out_color, a->out_depth, a->out_norm, a->out_alpha, a->out_extra,
+                  a->radii, a->geom, a->img, a->bin, a->sort, a->ctrl})) {
+    set_error("device pointers must be 16-byte aligned"); return IGS_ERR_INVALID;
+  }
   return IGS_OK;
 }
 
@@ -125,16 +139,8 @@ static PreArgs make_pre(const IgsFwdArgs* a) {
   p.radii = a->radii;
   p.splat = (float4*)(g + gl.splat);
   p.tiles_touched = (uint32_t*)(g + gl.tiles_touched);
-  p.point_offsets = (uint32_t*)(g + gl.point_offsets);
   p.clamped = (uint8_t*)(g + gl.clamped);
-  p.block_total = (uint32_t*)(c + cl.scan_state);
-  p.block_prefix = p.block_total + (a->P + PRE_THREADS - 1) / PRE_THREADS;
-  p.header = (CtrlHeader*)(c + cl.header);
-  p.num_rendered_host = device_view_of_pinned(a->num_rendered_pinned);
   p.tile_count = (uint32_t*)(c + cl.tile_count);
-  p.tile_cursor = (uint32_t*)(c + cl.tile_cursor);
-  p.ranges = (uint2*)((char*)a->img + ImgLayout(a->W, a->H).ranges);
-  p.tile_order = (uint32_t*)((char*)a->img + ImgLayout(a->W, a->H).tile_order);
   return p;
 }
 
@@ -154,31 +160,33 @@ static BinArgs make_bin(const IgsFwdArgs* a) {
   ba.radii = a->radii;
   ba.splat = (const float4*)(g + gl.splat);
   ba.tiles_touched = (const uint32_t*)(g + gl.tiles_touched);
-  ba.point_offsets = (uint32_t*)(g + gl.point_offsets);
-  ba.block_prefix = (const uint32_t*)(c + cl.scan_state) + (a->P + PRE_THREADS - 1) / PRE_THREADS;
   ba.header = (CtrlHeader*)(c + cl.header);
+  ba.num_rendered_host = device_view_of_pinned(a->num_rendered_pinned);
+  ba.tile_count = (uint32_t*)(c + cl.tile_count);
   ba.tile_cursor = (uint32_t*)(c + cl.tile_cursor);
-  ba.ranges = (const uint2*)(im + il.ranges);
+  ba.ranges = (uint2*)(im + il.ranges);
+  ba.tile_order = (uint32_t*)(im + il.tile_order);
+  ba.info = (uint32_t*)(im + il.info);
   ba.pairs = (unsigned long long*)(so + sl.pairs);
+  ba.pairs2 = (unsigned long long*)(so + sl.pairs2);
   ba.point_list = (uint32_t*)(b + bl.point_list);
-  ba.keys = (uint64_t*)(b + bl.keys);
+  ba.keys = a->write_keys ? (uint64_t*)(b + bl.keys) : nullptr;
   return ba;
 }
 
-static int run_bin_render(const IgsFwdArgs* a, cudaStream_t s, bool rerun = false) {
+static int run_bin_render(const IgsFwdArgs* a, cudaStream_t s) {
   const ImgLayout il(a->W, a->H);
   char* im = (char*)a->img;
   const bool debug = a->debug != 0;
-  BinArgs ba = make_bin(a);
-  if (rerun) ba.block_prefix = nullptr; // point_offsets were made global by the first pass
-  launch_binning(ba, s);
+  const BinArgs ba = make_bin(a);
+  if (int r = check_cuda(launch_binning(ba, s), "binning launch")) return r;
   if (int r = stage_check(debug, s, "binning (duplicate/tile sort)")) return r;
 
   RenderArgs ra{};
   ra.W = a->W; ra.H = a->H; ra.ED = a->ED; ra.grid_x = ba.grid_x; ra.grid_y = ba.grid_y;
   ra.header = ba.header;
   ra.ranges = ba.ranges;
-  ra.tile_order = (const uint32_t*)(im + il.tile_order);
+  ra.tile_order = ba.tile_order;
   ra.point_list = ba.point_list;
   ra.splat = ba.splat;
   ra.extra_attrs = a->extra_attrs;
@@ -188,12 +196,12 @@ static int run_bin_render(const IgsFwdArgs* a, cudaStream_t s, bool rerun = fals
   ra.n_contrib = (uint32_t*)(im + il.n_contrib);
   ra.norm_len = (float*)(im + il.norm_len);
   ra.normalize = a->normalize_norm != 0;
-  launch_render(ra, s);
+  if (int r = check_cuda(launch_render(ra, s), "render launch")) return r;
   prof_mark(5, s);
   return stage_check(debug, s, "render");
 }
 
-// zero the scan state, the tile counts and the header
+// zero the header, the tile counts and the tile cursors
 static int reset_ctrl(const IgsFwdArgs* a, cudaStream_t s) {
   const CtrlLayout cl(a->P, a->W, a->H);
   return check_cuda(cudaMemsetAsync(a->ctrl, 0, cl.zeroed(), s), "memset ctrl");
@@ -210,6 +218,7 @@ const char* igs_last_error(void) { return g_err; }
 
 size_t igs_geom_bytes(int32_t P) { return GeomLayout(P).total; }
 size_t igs_img_bytes(int32_t W, int32_t H) { return ImgLayout(W, H).total; }
+size_t igs_img_info_offset(int32_t W, int32_t H) { return ImgLayout(W, H).info; }
 size_t igs_bin_bytes(int64_t capacity) { return BinLayout(capacity).total; }
 size_t igs_sort_bytes(int64_t capacity) { return SortLayout(capacity).total; }
 size_t igs_ctrl_bytes(int32_t P, int32_t W, int32_t H) { return CtrlLayout(P, W, H).total; }
@@ -244,28 +253,29 @@ int igs_forward(const IgsFwdArgs* a, igs_stream_t stream, int64_t* num_rendered)
     return stage_check(debug, s, "empty forward");
   }
   const PreArgs pa = make_pre(a);
+  int32_t* const slot_dev = device_view_of_pinned(a->num_rendered_pinned);
   volatile int32_t* const slot = (volatile int32_t*)a->num_rendered_pinned;
-  if (pa.num_rendered_host) *slot = -1; // the preprocess kernel posts the count here (device-mapped pinned memory)
+  if (slot_dev) *slot = -1; // the duplicate kernel's service CTA posts the count here (device-mapped pinned memory)
   prof_mark(0, s);
-  launch_preprocess(pa, s);
+  if (int r = check_cuda(launch_preprocess(pa, s), "preprocess launch")) return r;
   prof_mark(1, s);
   if (int r = stage_check(debug, s, "preprocess")) return r;
-  cudaEvent_t ev = g_event.get();
-  if (!pa.num_rendered_host) { // slot not device-mapped: a copy-engine transfer and an event right behind it
-    if (int r = check_cuda(cudaMemcpyAsync(a->num_rendered_pinned, &pa.header->num_rendered, sizeof(int32_t),
-                                           cudaMemcpyDeviceToHost, s), "copy num_rendered")) return r;
-    if (int r = check_cuda(cudaEventRecord(ev, s), "event record")) return r;
-  }
   // speculative second half: sized by capacity, bounded on the device by num_rendered
   if (int r = run_bin_render(a, s)) return r;
-  if (a->defer_count && pa.num_rendered_host) {
+  if (a->defer_count && slot_dev) {
     // the caller reads the posted count later (igs_forward_count, or the slot itself: -1 = not
     // there yet) and holds it against the capacity; everything is queued, nothing on the device
     // depends on the host
     if (num_rendered) *num_rendered = -1;
     return IGS_OK;
   }
-  if (!pa.num_rendered_host) {
+  if (!slot_dev) { // slot not device-mapped: a copy-engine transfer behind the frame, and a wait for it
+    const CtrlLayout cl(a->P, a->W, a->H);
+    const CtrlHeader* h = (const CtrlHeader*)((const char*)a->ctrl + cl.header);
+    if (int r = check_cuda(cudaMemcpyAsync(a->num_rendered_pinned, &h->num_rendered, sizeof(int32_t),
+                                           cudaMemcpyDeviceToHost, s), "copy num_rendered")) return r;
+    cudaEvent_t ev = g_event.get();
+    if (int r = check_cuda(cudaEventRecord(ev, s), "event record")) return r;
     if (int r = check_cuda(cudaEventSynchronize(ev), "wait num_rendered")) return r;
   }
   return igs_forward_count(a, stream, num_rendered);
@@ -299,15 +309,23 @@ int igs_forward_count(const IgsFwdArgs* a, igs_stream_t stream, int64_t* num_ren
 }
 
 int igs_forward_bin_render(const IgsFwdArgs* a, igs_stream_t stream) {
+  // After IGS_ERR_CAPACITY: same geom / img / ctrl, bigger bin / sort.  The frame is queued again
+  // from the top (every kernel leaves [ctrl] clean, also when the frame did not fit, so the tile
+  // counts of the first attempt are gone); the per-Gaussian kernel is a tenth of a frame, and a
+  // frame that outgrows 2x the largest count seen so far is rare.
   if (int r = validate_fwd(a)) return r;
-  cudaStream_t s = (cudaStream_t)stream;
-  // same geom / img / ctrl as the igs_forward that overflowed (tile ranges and counts are
-  // still valid), bigger bin / sort: clear the overflow flag, rewind the tile cursors
-  const BinArgs ba = make_bin(a);
-  if (int r = check_cuda(cudaMemsetAsync(&ba.header->overflow, 0, sizeof(uint32_t), s), "clear overflow")) return r;
-  if (int r = check_cuda(cudaMemsetAsync(&ba.header->render_ticket, 0, sizeof(uint32_t), s), "clear ticket")) return r;
-  launch_reset_cursors(ba, s);
-  return run_bin_render(a, s, true);
+  IgsFwdArgs b = *a;
+  b.ctrl_clean = 1;
+  b.defer_count = 0;
+  return igs_forward(&b, stream, nullptr);
+}
+
+int igs_point_offsets(int32_t P, void* geom, igs_stream_t stream) {
+  if (P < 0 || (P > 0 && !geom)) { set_error("igs_point_offsets: bad arguments"); return IGS_ERR_INVALID; }
+  const GeomLayout gl(P);
+  launch_point_offsets(P, (const uint32_t*)((char*)geom + gl.tiles_touched), (uint32_t*)((char*)geom + gl.point_offsets),
+                       (cudaStream_t)stream);
+  return stage_check(false, (cudaStream_t)stream, "point_offsets");
 }
 
 int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
@@ -317,6 +335,13 @@ int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
   if (!a->accum || !a->geom || !a->img || !a->bin || !a->out_alpha || !a->dL_dcolor || !a->dL_ddepth ||
       !a->dL_dnorm || !a->dL_dalpha || (a->ED > 0 && !a->dL_dextra) || (a->normalize_norm && !a->out_norm)) {
     set_error("null buffer"); return IGS_ERR_INVALID;
+  }
+  if (misaligned({a->means3D, a->shs, a->colors_precomp, a->scales, a->rotations, a->cov3Ds_precomp, a->norm3Ds_precomp,
+                  a->extra_attrs, a->radii, a->geom, a->img, a->bin, a->out_alpha, a->out_norm, a->dL_dcolor, a->dL_ddepth,
+                  a->dL_dnorm, a->dL_dalpha, a->dL_dextra, a->accum, a->dL_dmeans2D, a->dL_dcolors, a->dL_dopacity,
+                  a->dL_dmeans3D, a->dL_dcov3D, a->dL_dnorm3D, a->dL_dsh, a->dL_dscales, a->dL_drotations,
+                  a->dL_dextra_attrs})) {
+    set_error("device pointers must be 16-byte aligned"); return IGS_ERR_INVALID;
   }
   cudaStream_t s = (cudaStream_t)stream;
   const bool debug = a->debug != 0;
@@ -346,7 +371,8 @@ int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
   ra.ticket = (uint32_t*)((char*)a->accum + accum_ticket_offset(a->P, a->ED));
   ra.accum_extra = a->ED > 1 ? (float*)((char*)a->accum + align_up((size_t)a->P * ACC_F * sizeof(float))) : nullptr;
   prof_mark(6, s);
-  if (a->num_rendered > 0) launch_render_backward(ra, s);
+  if (a->num_rendered != 0) // (< 0: the caller does not know the count; the kernel finds empty lists by itself)
+    if (int r = check_cuda(launch_render_backward(ra, s), "render backward launch")) return r;
   prof_mark(7, s);
   if (int r = stage_check(debug, s, "render backward")) return r;
 
@@ -366,7 +392,7 @@ int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
   pa.dL_dmeans3D = a->dL_dmeans3D; pa.dL_dcov3D = a->dL_dcov3D; pa.dL_dnorm3D = a->dL_dnorm3D;
   pa.dL_dsh = a->dL_dsh; pa.dL_dscales = a->dL_dscales; pa.dL_drotations = a->dL_drotations;
   pa.dL_dextra_attrs = a->dL_dextra_attrs;
-  launch_preprocess_backward(pa, s);
+  if (int r = check_cuda(launch_preprocess_backward(pa, s), "preprocess backward launch")) return r;
   prof_mark(8, s);
   return stage_check(debug, s, "preprocess backward");
 }

@@ -45,7 +45,7 @@ struct GeomLayout {
 };
 
 struct ImgLayout {
-  size_t ranges, n_contrib, tile_order, norm_len, total;
+  size_t ranges, n_contrib, tile_order, norm_len, info, total;
   __host__ __device__ ImgLayout(int W, int H) {
     size_t T = (size_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
     size_t o = 0;
@@ -53,6 +53,7 @@ struct ImgLayout {
     tile_order = o; o = align_up(o + (T ? T : 1) * sizeof(uint32_t)); // tiles, longest list first
     n_contrib = o;  o = align_up(o + (size_t)(W * H > 0 ? W * H : 1) * sizeof(uint32_t));
     norm_len = o;   o = align_up(o + (size_t)(W * H > 0 ? W * H : 1) * sizeof(float)); // |n| per pixel (fused normalize)
+    info = o;       o = align_up(o + 4 * sizeof(uint32_t)); // {num_rendered of this frame, -, -, -}: kept with the state
     total = o;
   }
 };
@@ -68,10 +69,11 @@ struct BinLayout { // sorted result, kept for backward
 };
 
 struct SortLayout { // unsorted (depth|id) pairs grouped by tile, scratch
-  size_t pairs, total;
+  size_t pairs, pairs2, total;
   __host__ __device__ explicit SortLayout(int64_t cap) {
     size_t c = (size_t)(cap > 0 ? cap : 1), o = 0;
-    pairs = o;  o = align_up(o + c * sizeof(uint64_t));
+    pairs = o;   o = align_up(o + c * sizeof(uint64_t));
+    pairs2 = o;  o = align_up(o + c * sizeof(uint64_t)); // second level of the sort of segments beyond TS_CAP
     total = o;
   }
 };
@@ -80,31 +82,31 @@ constexpr int PRE_THREADS = 512;   // Gaussians per preprocess / duplicate CTA
 // Per-tile counters and cursors live one per 128-byte line: the L2 atomic units then work on
 // ~T different lines instead of T/32 (measured: contended REDs to neighbouring words serialise).
 constexpr int CNT_STRIDE = 32;     // in uint32 words
-constexpr int HIST_SMEM_MAX_TILES = 11264; // CTA-local tile histogram fits 44 KB of shared memory
+// CTA-local tile histograms live in dynamic shared memory (4 bytes per tile, opted in beyond 48 KB):
+// 49152 tiles = 192 KB covers images up to ~3500x3500; larger ones count in global memory
+constexpr int HIST_SMEM_MAX_TILES = 49152;
 
 struct CtrlHeader {
-  uint32_t num_rendered;  // written by the preprocess CTA that owns the last Gaussians
-  uint32_t overflow;      // num_rendered > capacity
-  uint32_t ticket;        // dynamic CTA ids of the preprocess kernel (scan order = start order)
-  uint32_t done;          // preprocess CTAs that have finished; the last one scans the tile counts
+  uint32_t num_rendered;  // sum of the tile counts, written by the service CTA of the duplicate kernel
+  uint32_t overflow;      // num_rendered > capacity: the kernels behind it do nothing
   uint32_t render_ticket; // next (tile, 8x4 block) unit of the persistent render kernel
-  uint32_t pad[3];
+  uint32_t pad[5];
 };
 
 struct CtrlLayout {
-  size_t header, scan_state, tile_count, tile_cursor, total;
+  size_t header, tile_count, tile_cursor, total;
   __host__ __device__ CtrlLayout(int P, int W, int H) {
+    (void)P;
     size_t o = 0;
-    const int pre_blocks = (P + PRE_THREADS - 1) / PRE_THREADS;
     const size_t T = (size_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
     header = o;       o = align_up(o + sizeof(CtrlHeader));
-    scan_state = o;   o = align_up(o + (size_t)(pre_blocks ? pre_blocks : 1) * sizeof(unsigned long long));
     tile_count = o;   o = align_up(o + (T ? T : 1) * CNT_STRIDE * sizeof(uint32_t));
     tile_cursor = o;  o = align_up(o + (T ? T : 1) * CNT_STRIDE * sizeof(uint32_t));
     total = o;
   }
-  // everything before tile_cursor is zeroed at the start of a frame
-  __host__ __device__ size_t zeroed() const { return tile_cursor; }
+  // a frame starts from an all-zero block; the kernels put every word back to zero when they are
+  // done with it (tile_sort_kernel: counts and cursors of its tile), so a steady-state frame needs no memset
+  __host__ __device__ size_t zeroed() const { return total; }
 };
 
 // [P][16] accumulators | [P][ED-1] side array | unit ticket of the persistent backward kernel
@@ -148,10 +150,16 @@ void count_launch(int n = 1);
 // the attribute pdl_wait() returns immediately.)
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// Lets the NEXT kernel on the stream (if it was launched as a programmatic dependent) be scheduled
+// as soon as every CTA of this grid has started: its CTAs run their prologue (shared-memory
+// clears, constant loads) on whatever SM resources are free and then block in pdl_wait() until
+// this grid has completed.  Without it they are only scheduled as this grid's CTAs exit.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 template <class... KArgs, class... Args>
 inline cudaError_t launch_after(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
                                 Args&&... args) {
+  // (a launch error is returned AND stays in cudaGetLastError for the stage check that follows)
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
   // IGS_NO_PDL=1: plain stream order (griddepcontrol.wait is then a no-op); for debugging only

@@ -14,16 +14,8 @@ struct PreArgs {
   int32_t* radii;
   float4* splat;
   uint32_t* tiles_touched;
-  uint32_t* point_offsets;
   uint8_t* clamped;
-  uint32_t* block_total;   // [ceil(P/PRE_THREADS)] sum of tiles_touched per preprocess CTA
-  uint32_t* block_prefix;  // [same] exclusive scan of block_total (written by the last CTA)
-  CtrlHeader* header;
-  int32_t* num_rendered_host; // device view of the caller's pinned slot (NULL: the host copies it)
-  uint32_t* tile_count;   // [T*CNT_STRIDE] instances per tile (atomics), zeroed by the caller
-  uint32_t* tile_cursor;  // [T*CNT_STRIDE] next free slot of each tile segment (written by the last CTA)
-  uint2* ranges;          // [T] [start, end) of each tile in the sorted list, (0,0) if empty
-  uint32_t* tile_order;   // [T] tile ids, longest list first (the render kernels' launch order)
+  uint32_t* tile_count;   // [T*CNT_STRIDE] instances per tile (atomics); zero at the start of a frame
 };
 
 struct BinArgs {
@@ -32,14 +24,18 @@ struct BinArgs {
   const int32_t* radii;
   const float4* splat;
   const uint32_t* tiles_touched;
-  uint32_t* point_offsets;       // CTA-local inclusive scan from preprocess; made global here
-  const uint32_t* block_prefix;  // NULL on a re-run after IGS_ERR_CAPACITY (offsets already global)
   CtrlHeader* header;
-  uint32_t* tile_cursor;      // [T*CNT_STRIDE]
-  const uint2* ranges;        // [T]
+  int32_t* num_rendered_host; // device view of the caller's pinned slot (NULL: the host copies it)
+  uint32_t* info;             // [4] in the img workspace: {num_rendered, ...}, stays with the frame's state
+  uint32_t* tile_count;       // [T*CNT_STRIDE] instances per tile, from the preprocess kernel
+  uint32_t* tile_cursor;      // [T*CNT_STRIDE] slots handed out so far in each tile's segment (relative; absolute
+                              // when the counts do not fit shared memory, see tile_scan_kernel)
+  uint2* ranges;              // [T] [start, end) of each tile in the sorted list, (0,0) if empty
+  uint32_t* tile_order;       // [T] tile ids, longest list first (the render kernels' unit order)
   unsigned long long* pairs;  // [capacity] (depth bits << 32 | gaussian id), grouped by tile, unordered inside
+  unsigned long long* pairs2; // [capacity] scratch of the two-level sort of segments beyond TS_CAP
   uint32_t* point_list;       // [capacity] sorted
-  uint64_t* keys;             // [capacity] sorted (tile << 32 | depth bits)
+  uint64_t* keys;             // [capacity] sorted (tile << 32 | depth bits), or NULL: not wanted
 };
 
 struct RenderArgs {
@@ -95,12 +91,12 @@ struct BwdPreArgs {
 // {globaltimer at start, at end, smid | unit << 32} -- 3 words per unit, forward units first
 cudaError_t set_render_trace(unsigned long long* device_buffer);
 
-void launch_preprocess(const PreArgs& a, cudaStream_t s);
+cudaError_t launch_preprocess(const PreArgs& a, cudaStream_t s);
 void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s);
-void launch_binning(const BinArgs& a, cudaStream_t s);     // duplicate into tile segments + per-tile depth sort
-void launch_reset_cursors(const BinArgs& a, cudaStream_t s); // tile_cursor <- ranges.x (re-run after IGS_ERR_CAPACITY)
-void launch_render(const RenderArgs& a, cudaStream_t s);
-void launch_render_backward(const BwdRenderArgs& a, cudaStream_t s);
-void launch_preprocess_backward(const BwdPreArgs& a, cudaStream_t s);
+cudaError_t launch_binning(const BinArgs& a, cudaStream_t s);     // tile ranges, duplicate into tile segments, per-tile depth sort
+void launch_point_offsets(int P, const uint32_t* tiles_touched, uint32_t* point_offsets, cudaStream_t s);
+cudaError_t launch_render(const RenderArgs& a, cudaStream_t s);
+cudaError_t launch_render_backward(const BwdRenderArgs& a, cudaStream_t s);
+cudaError_t launch_preprocess_backward(const BwdPreArgs& a, cudaStream_t s);
 
 } // namespace igs

@@ -1,11 +1,13 @@
 // Stage 1 of the forward path: per-Gaussian preprocess (EWA projection, 3D->2D
-// covariance, SH->RGB, radius, tile rectangle) fused with the inclusive prefix
-// sum of tiles_touched (single-pass decoupled look-back), so that one launch
-// replaces the reference's preprocessCUDA + cub::DeviceScan::InclusiveSum
-// (reference forward.cu:203-316, rasterizer_impl.cu:280).  Also markVisible.
+// covariance, SH->RGB, radius, tile rectangle; reference forward.cu:203-316) fused
+// with the count of instances per tile that sizes the tile segments (the role of
+// cub::DeviceScan::InclusiveSum, rasterizer_impl.cu:280, in the reference: here
+// instances are placed by tile, not by Gaussian).  One thread per Gaussian, no
+// dependence between threads except the CTA-local tile histogram.  Also markVisible
+// and the on-request prefix sum of tiles_touched (the reference's point_offsets).
 //
 // Bound: HBM.  Algorithmic bytes per Gaussian: reads 44 (+12*(D+1)^2 SH),
-// writes 64 (splat record) + 4 radii + 4 tiles + 4 offsets (+1 clamp mask).
+// writes 64 (splat record) + 4 radii + 4 tiles (+1 clamp mask); 4 per instance of tile counting.
 #include "igs_common.cuh"
 #include "igs_kernels.cuh"
 #include "igs_math.cuh"
@@ -78,38 +80,21 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, int M, const float* __restr
   return make_float3(res[0], res[1], res[2]);
 }
 
-constexpr int ORDER_BUCKETS = 2 * PRE_THREADS;
-
-#ifdef IGS_PRE_TRACE
-__device__ unsigned long long g_pre_trace[8 * 4096];
-__device__ __forceinline__ unsigned long long pre_timer() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-  return t;
-}
-#define PRE_MARK(k) do { if (threadIdx.x == 0) g_pre_trace[8 * blockIdx.x + (k)] = pre_timer(); } while (0)
-#else
-#define PRE_MARK(k) do { } while (0)
-#endif
-
 template <bool USE_SH, bool HIST_SMEM>
 __global__ void __launch_bounds__(PRE_THREADS, 1024 / PRE_THREADS) preprocess_kernel(PreArgs a) {
   __shared__ float s_view[16], s_proj[16], s_cam[3];
-  __shared__ uint32_t s_warp_sum[PRE_THREADS / 32];
-  __shared__ uint32_t s_last;
   // CTA-local histogram of the instances per tile (HIST_SMEM: the launch gave us 4*T bytes):
   // one global RED per (CTA, non-empty tile) instead of one per instance
   extern __shared__ uint32_t s_hist[];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x;
   const int T = a.grid_x * a.grid_y;
+  pdl_launch_dependents(); // the duplicate kernel's CTAs may take their places (they wait for this grid to finish)
   if (HIST_SMEM)
     for (int t = tid; t < T; t += PRE_THREADS) s_hist[t] = 0u;
   pdl_wait(); // launched as a programmatic dependent of whatever precedes it on the stream
   if (tid < 16) { s_view[tid] = __ldg(a.viewmatrix + tid); s_proj[tid] = __ldg(a.projmatrix + tid); }
   if (tid < 3) s_cam[tid] = __ldg(a.campos + tid);
-  PRE_MARK(0);
   __syncthreads();
-  PRE_MARK(1);
   const int bid = (int)blockIdx.x;
 
   const int idx = bid * PRE_THREADS + tid;
@@ -198,165 +183,16 @@ __global__ void __launch_bounds__(PRE_THREADS, 1024 / PRE_THREADS) preprocess_ke
     a.tiles_touched[idx] = tiles;
   }
 
-  PRE_MARK(2);
-  // block inclusive scan of `tiles`
-  uint32_t incl = tiles;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t n = __shfl_up_sync(0xffffffffu, incl, o);
-    if (lane >= o) incl += n;
-  }
-  if (lane == 31) s_warp_sum[warp] = incl;
-  __syncthreads();
-  if (warp == 0) {
-    uint32_t w = lane < PRE_THREADS / 32 ? s_warp_sum[lane] : 0u;
-    uint32_t wi = w;
-#pragma unroll
-    for (int o = 1; o < PRE_THREADS / 32; o <<= 1) {
-      const uint32_t n = __shfl_up_sync(0xffffffffu, wi, o);
-      if (lane >= o) wi += n;
-    }
-    const uint32_t total = __shfl_sync(0xffffffffu, wi, PRE_THREADS / 32 - 1);
-    if (lane < PRE_THREADS / 32) s_warp_sum[lane] = wi - w; // exclusive warp offsets
-    // no look-back chain: the CTA publishes its total, the last CTA scans the totals, and the
-    // duplicate kernel adds the CTA's prefix to these CTA-local offsets
-    if (lane == 0) a.block_total[bid] = total;
-  }
-  __syncthreads();
-  PRE_MARK(3);
-  if (idx < a.P) a.point_offsets[idx] = s_warp_sum[warp] + incl;
-  if (HIST_SMEM) { // (the barrier above ordered every thread's shared-memory atomics)
+  // No prefix sum here: instances are placed by tile (per-tile counts -> ranges -> cursors,
+  // igs_binning.cu), so the reference's point_offsets (InclusiveSum, rasterizer_impl.cu:280) is not
+  // on the path; igs_point_offsets produces it on request.  num_rendered is the sum of the tile counts.
+  if (HIST_SMEM) {
+    __syncthreads();
     for (int t = tid; t < T; t += PRE_THREADS) {
       const uint32_t c = s_hist[t];
       if (c) atomicAdd(a.tile_count + (size_t)t * CNT_STRIDE, c);
     }
   }
-
-  // ---- the CTA that finishes last turns the tile counts into tile ranges ------------------
-  // (reference identifyTileRanges, rasterizer_impl.cu:116-138 + the memset at :313: the
-  // range of a tile is [exclusive prefix of the counts, +count), (0,0) for an empty tile)
-  __threadfence();
-  __syncthreads();
-  PRE_MARK(4);
-  if (tid == 0) s_last = atomicAdd(&a.header->done, 1u) == gridDim.x - 1 ? 1u : 0u;
-  __syncthreads();
-  PRE_MARK(5);
-  if (!s_last) return;
-  __threadfence();
-  // (1) tile counts: one L2 round trip into shared memory (all requests in flight together);
-  //     later phases read them from there.  Beyond HIST_SMEM_MAX_TILES they stay in L2.
-  //     The counters go back to zero as they are read: the next frame needs no memset of [ctrl].
-  if (HIST_SMEM) {
-    for (int t = tid; t < T; t += PRE_THREADS) {
-      s_hist[t] = __ldcg(a.tile_count + (size_t)t * CNT_STRIDE);
-      a.tile_count[(size_t)t * CNT_STRIDE] = 0u;
-    }
-  }
-  if (tid == 0) { a.header->done = 0u; a.header->render_ticket = 0u; }
-#define TILE_CNT(t) (HIST_SMEM ? s_hist[t] : __ldcg(a.tile_count + (size_t)(t) * CNT_STRIDE))
-  // (2) CTA totals of tiles_touched -> exclusive prefixes (added to point_offsets by the
-  //     duplicate kernel), num_rendered, overflow flag
-  const int nb = (int)gridDim.x;
-  const int bper = (nb + PRE_THREADS - 1) / PRE_THREADS;
-  const int b0 = min(nb, tid * bper), b1 = min(nb, b0 + bper);
-  uint32_t bsum = 0;
-  for (int b = b0; b < b1; b++) bsum += __ldcg(a.block_total + b);
-  uint32_t binc = bsum;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t n = __shfl_up_sync(0xffffffffu, binc, o);
-    if (lane >= o) binc += n;
-  }
-  __syncthreads(); // s_warp_sum is reused; s_hist is complete
-  if (lane == 31) s_warp_sum[warp] = binc;
-  __syncthreads();
-  {
-    uint32_t run = binc - bsum, all = 0;
-    for (int w = 0; w < PRE_THREADS / 32; w++) {
-      if (w < warp) run += s_warp_sum[w];
-      all += s_warp_sum[w];
-    }
-    if (bper == 1) { // P <= PRE_THREADS^2: this thread's one total is already in a register
-      if (b0 < b1) a.block_prefix[b0] = run;
-    } else {
-      for (int b = b0; b < b1; b++) {
-        a.block_prefix[b] = run;
-        run += __ldcg(a.block_total + b);
-      }
-    }
-    if (tid == 0) {
-      a.header->num_rendered = all;
-      a.header->overflow = (int64_t)all > a.capacity ? 1u : 0u;
-      // straight into the caller's pinned host slot: a 4-byte copy-engine transfer between two
-      // kernels costs ~12 us of stream time on B200, a posted store costs nothing
-      // No system-scope fence after it: the store is posted to the host at once, while a
-      // __threadfence_system() here held the whole CTA at its next barrier for the PCIe round trip
-      // (3-4 us of every frame, measured with IGS_PRE_TRACE); the host polls this slot.
-      if (a.num_rendered_host) *(volatile int32_t*)a.num_rendered_host = (int32_t)all;
-    }
-  }
-  // (3) tile counts -> ranges and cursors
-  const int per = (T + PRE_THREADS - 1) / PRE_THREADS;
-  const int t0 = min(T, tid * per), t1 = min(T, t0 + per);
-  uint32_t sum = 0, cmax = 0;
-  for (int t = t0; t < t1; t++) { const uint32_t c = TILE_CNT(t); sum += c; cmax = max(cmax, c); }
-  uint32_t inc = sum;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
-    if (lane >= o) inc += n;
-  }
-  __shared__ uint32_t s_bucket[ORDER_BUCKETS];
-  __shared__ uint32_t s_max[PRE_THREADS / 32];
-  cmax = __reduce_max_sync(0xffffffffu, cmax);
-  __syncthreads(); // s_warp_sum is reused
-  if (lane == 31) s_warp_sum[warp] = inc;
-  if (lane == 0) s_max[warp] = cmax;
-  for (int b = tid; b < ORDER_BUCKETS; b += PRE_THREADS) s_bucket[b] = 0u;
-  __syncthreads();
-  uint32_t run = inc - sum;
-  for (int w = 0; w < warp; w++) run += s_warp_sum[w];
-#pragma unroll
-  for (int w = 0; w < PRE_THREADS / 32; w++) cmax = max(cmax, s_max[w]);
-  // ---- launch order of the render kernels: tiles with the longest lists first (their warps
-  // are the critical path), by one counting pass over ORDER_BUCKETS count classes ----
-  const float qs = (float)(ORDER_BUCKETS - 1) / (float)max(cmax, 1u);
-#define ORDER_BUCKET(c) ((ORDER_BUCKETS - 1) - min(ORDER_BUCKETS - 1, (int)((float)(c) * qs)))
-  for (int t = t0; t < t1; t++) {
-    const uint32_t c = TILE_CNT(t);
-    a.tile_cursor[(size_t)t * CNT_STRIDE] = run;
-    a.ranges[t] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
-    run += c;
-    atomicAdd(&s_bucket[ORDER_BUCKET(c)], 1u);
-  }
-  __syncthreads();
-  { // exclusive scan of the bucket sizes (ORDER_BUCKETS == 2 * PRE_THREADS: two per thread)
-    const uint32_t c0 = s_bucket[2 * tid], c1 = s_bucket[2 * tid + 1];
-    uint32_t in2 = c0 + c1;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t n = __shfl_up_sync(0xffffffffu, in2, o);
-      if (lane >= o) in2 += n;
-    }
-    if (lane == 31) s_max[warp] = in2;
-    __syncthreads();
-    uint32_t base = in2 - (c0 + c1);
-    for (int w = 0; w < warp; w++) base += s_max[w];
-    s_bucket[2 * tid] = base;
-    s_bucket[2 * tid + 1] = base + c0;
-  }
-  __syncthreads();
-  for (int t = t0; t < t1; t++) {
-    const uint32_t slot = atomicAdd(&s_bucket[ORDER_BUCKET(TILE_CNT(t))], 1u);
-    a.tile_order[slot] = (uint32_t)t;
-  }
-  if (!HIST_SMEM) { // the counts were read from global memory up to here
-    __syncthreads();
-    for (int t = tid; t < T; t += PRE_THREADS) a.tile_count[(size_t)t * CNT_STRIDE] = 0u;
-  }
-#undef TILE_CNT
-  PRE_MARK(6);
-#undef ORDER_BUCKET
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
@@ -370,26 +206,29 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, co
   present[idx] = !(vz <= NEAR_Z);
 }
 
-void launch_preprocess(const PreArgs& a, cudaStream_t s) {
-  if (a.P <= 0) return;
+cudaError_t launch_preprocess(const PreArgs& a, cudaStream_t s) {
+  if (a.P <= 0) return cudaSuccess;
   const int blocks = (a.P + PRE_THREADS - 1) / PRE_THREADS;
   const int T = a.grid_x * a.grid_y;
   const size_t hist = (size_t)T * sizeof(uint32_t);
-  if (T <= HIST_SMEM_MAX_TILES) {
-    if (a.shs) launch_after(preprocess_kernel<true, true>, dim3(blocks), dim3(PRE_THREADS), hist, s, a);
-    else launch_after(preprocess_kernel<false, true>, dim3(blocks), dim3(PRE_THREADS), hist, s, a);
-  } else { // images beyond ~1700x1700: count straight into global memory
-    if (a.shs) launch_after(preprocess_kernel<true, false>, dim3(blocks), dim3(PRE_THREADS), 0, s, a);
-    else launch_after(preprocess_kernel<false, false>, dim3(blocks), dim3(PRE_THREADS), 0, s, a);
-  }
+  // the histogram may need more than the 48 KB a kernel gets without asking
+  static const cudaError_t optin = [] {
+    const int bytes = HIST_SMEM_MAX_TILES * (int)sizeof(uint32_t);
+    cudaError_t e = cudaFuncSetAttribute(preprocess_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(preprocess_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    return e;
+  }();
+  if (optin != cudaSuccess) return optin;
   count_launch();
+  if (T <= HIST_SMEM_MAX_TILES) {
+    if (a.shs) return launch_after(preprocess_kernel<true, true>, dim3(blocks), dim3(PRE_THREADS), hist, s, a);
+    return launch_after(preprocess_kernel<false, true>, dim3(blocks), dim3(PRE_THREADS), hist, s, a);
+  }
+  // images beyond ~3500x3500: count straight into global memory
+  if (a.shs) return launch_after(preprocess_kernel<true, false>, dim3(blocks), dim3(PRE_THREADS), 0, s, a);
+  return launch_after(preprocess_kernel<false, false>, dim3(blocks), dim3(PRE_THREADS), 0, s, a);
 }
-
-#ifdef IGS_PRE_TRACE
-extern "C" int igs_pre_trace_read(unsigned long long* host, int n) {
-  return (int)cudaMemcpyFromSymbol(host, g_pre_trace, sizeof(unsigned long long) * n);
-}
-#endif
 
 void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s) {
   if (P <= 0) return;

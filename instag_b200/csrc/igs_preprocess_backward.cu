@@ -129,6 +129,7 @@ template <bool USE_SH>
 __global__ void __launch_bounds__(256) preprocess_backward_kernel(BwdPreArgs a) {
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   const int tid = threadIdx.x;
+  pdl_launch_dependents();
   if (tid < 16) { s_view[tid] = __ldg(a.viewmatrix + tid); s_proj[tid] = __ldg(a.projmatrix + tid); }
   if (tid < 3) s_cam[tid] = __ldg(a.campos + tid);
   pdl_wait(); // the accumulator rows of the render-backward kernel
@@ -323,12 +324,12 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(BwdPreArgs a) 
   reinterpret_cast<float4*>(a.dL_drotations)[idx] = drot;
 }
 
-void launch_preprocess_backward(const BwdPreArgs& a, cudaStream_t s) {
-  if (a.P <= 0) return;
+cudaError_t launch_preprocess_backward(const BwdPreArgs& a, cudaStream_t s) {
+  if (a.P <= 0) return cudaSuccess;
   const int blocks = (a.P + 255) / 256;
-  if (a.shs) launch_after(preprocess_backward_kernel<true>, dim3(blocks), dim3(256), 0, s, a);
-  else launch_after(preprocess_backward_kernel<false>, dim3(blocks), dim3(256), 0, s, a);
   count_launch();
+  if (a.shs) return launch_after(preprocess_backward_kernel<true>, dim3(blocks), dim3(256), 0, s, a);
+  return launch_after(preprocess_backward_kernel<false>, dim3(blocks), dim3(256), 0, s, a);
 }
 
 } // namespace igs

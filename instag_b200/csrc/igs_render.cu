@@ -16,8 +16,8 @@
 //  * ids are prefetched two chunks ahead and the cull data one chunk ahead, so
 //    the list walk never waits for an id -> record pointer chase;
 //  * a warp stops as soon as its 32 pixels are saturated (the reference only
-//    votes per CTA, forward.cu:380), and 2-warp CTAs (4096 of them at 512^2)
-//    let the hardware scheduler balance the SMs at 1/8-tile granularity.
+//    votes per CTA, forward.cu:380); the kernel is persistent (4-warp CTAs, as
+//    many as fit) and every warp pulls units from one ticket, longest lists first.
 // None of this changes a pixel: the per-pixel arithmetic below is the
 // reference's, with the same FMA contraction (igs_common.cuh gauss_power).
 //
@@ -64,6 +64,7 @@ __global__ void __launch_bounds__(RT) render_kernel(RenderArgs a) {
   __shared__ uint32_t s_id[ED_T < 0 ? RW : 1][32];
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  pdl_launch_dependents();
   pdl_wait(); // the sorted tile lists
   if (a.header->overflow) return;
   const int num_units = a.grid_x * a.grid_y * 8;
@@ -252,16 +253,16 @@ static int resident_ctas(K kernel, int threads) {
 
 cudaError_t set_render_trace(unsigned long long* p) { return cudaMemcpyToSymbol(g_trace, &p, sizeof p); }
 
-void launch_render(const RenderArgs& a, cudaStream_t s) {
-  if (a.W <= 0 || a.H <= 0) return;
+cudaError_t launch_render(const RenderArgs& a, cudaStream_t s) {
+  if (a.W <= 0 || a.H <= 0) return cudaSuccess;
   static const int cap0 = resident_ctas(render_kernel<0>, RT), cap1 = resident_ctas(render_kernel<1>, RT),
                    capx = resident_ctas(render_kernel<-1>, RT);
   const int units = a.grid_x * a.grid_y * 8;
   const int want = (units + RW - 1) / RW;
-  if (a.ED == 0) launch_after(render_kernel<0>, dim3(min(want, cap0)), dim3(RT), 0, s, a);
-  else if (a.ED == 1) launch_after(render_kernel<1>, dim3(min(want, cap1)), dim3(RT), 0, s, a);
-  else launch_after(render_kernel<-1>, dim3(min(want, capx)), dim3(RT), 0, s, a);
   count_launch();
+  if (a.ED == 0) return launch_after(render_kernel<0>, dim3(min(want, cap0)), dim3(RT), 0, s, a);
+  if (a.ED == 1) return launch_after(render_kernel<1>, dim3(min(want, cap1)), dim3(RT), 0, s, a);
+  return launch_after(render_kernel<-1>, dim3(min(want, capx)), dim3(RT), 0, s, a);
 }
 
 } // namespace igs

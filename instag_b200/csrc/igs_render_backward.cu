@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
   // parked blend weights [0] and g = G*dL/dalpha [1] of up to PEND splats; pixel p of slot s sits
   // in column p ^ ((s & 1) << 4) so that both the scalar stores and the 16-byte fragment loads are
   // bank-conflict free
-  __shared__ __align__(16) float s_wg[BW][2][PEND][32];
+  __shared__ __align__(128) float s_wg[BW][2][PEND][32]; // (the swizzle works on address bits: keep 128-byte alignment)
   // 512-byte stride per warp (PEND = 16 records used): the fill level of a warp's queue is then
   // (address & 511) >> 4, with no base address to keep in (or recompute into) a register
   __shared__ __align__(512) float4 s_pend[BW][32]; // {mean.x, mean.y, gaussian id bits, -}
@@ -92,6 +92,7 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
   __shared__ float4 s_bm[2][32];
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  pdl_launch_dependents();
   pdl_wait(); // whatever ran before on the stream (the forward, the caller's loss kernels) is complete
   const int num_units = a.grid_x * a.grid_y * 8;
   const int ED = ED_T < 0 ? a.ED : ED_T;
@@ -384,17 +385,17 @@ static int resident_ctas_bwd(K kernel, int threads) {
   return (sms > 0 ? sms : 148) * (per_sm > 0 ? per_sm : 1);
 }
 
-void launch_render_backward(const BwdRenderArgs& a, cudaStream_t s) {
-  if (a.W <= 0 || a.H <= 0) return;
+cudaError_t launch_render_backward(const BwdRenderArgs& a, cudaStream_t s) {
+  if (a.W <= 0 || a.H <= 0) return cudaSuccess;
   static const int cap0 = resident_ctas_bwd(render_backward_kernel<0>, BT),
                    cap1 = resident_ctas_bwd(render_backward_kernel<1>, BT),
                    capx = resident_ctas_bwd(render_backward_kernel<-1>, BT);
   const int units = a.grid_x * a.grid_y * 8;
   const int want = (units + BW - 1) / BW;
-  if (a.ED == 0) launch_after(render_backward_kernel<0>, dim3(min(want, cap0)), dim3(BT), 0, s, a);
-  else if (a.ED == 1) launch_after(render_backward_kernel<1>, dim3(min(want, cap1)), dim3(BT), 0, s, a);
-  else launch_after(render_backward_kernel<-1>, dim3(min(want, capx)), dim3(BT), 0, s, a);
   count_launch();
+  if (a.ED == 0) return launch_after(render_backward_kernel<0>, dim3(min(want, cap0)), dim3(BT), 0, s, a);
+  if (a.ED == 1) return launch_after(render_backward_kernel<1>, dim3(min(want, cap1)), dim3(BT), 0, s, a);
+  return launch_after(render_backward_kernel<-1>, dim3(min(want, capx)), dim3(BT), 0, s, a);
 }
 
 } // namespace igs

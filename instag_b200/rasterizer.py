@@ -24,8 +24,9 @@ def cpu_deep_copy_tuple(input_tuple):
 
 
 class _DeviceScratch:
-    """Per-device reusable scratch: sort ping-pong partner, look-back state,
-    gradient accumulators, the pinned num_rendered slot, a capacity estimate."""
+    """Reusable scratch of one (device, stream, host thread): the unsorted instance words, the
+    control block (tile counters and cursors), the gradient accumulators, the pinned num_rendered
+    slot, and the instance capacity to allocate for each (P, H, W) seen so far."""
 
     def __init__(self, device):
         self.device = device
@@ -130,9 +131,10 @@ class GaussianRasterizationSettings(NamedTuple):
 def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier,
                     cov3Ds_precomp, norm3Ds_precomp, extra_attrs, ED, viewmatrix, projmatrix, tanfovx,
                     tanfovy, image_height, image_width, sh, sh_degree, campos, prefiltered, debug,
-                    normalize_norm=False):
+                    normalize_norm=False, write_keys=False):
     """Equivalent of _C.rasterize_gaussians (DGR rasterize_points.cu:35-133).  normalize_norm: the
-    kernel also applies the F.normalize(norm, dim=0) of DGR diff_gauss/__init__.py:48."""
+    kernel also applies the F.normalize(norm, dim=0) of DGR diff_gauss/__init__.py:48.  write_keys:
+    also leave the reference's sorted 64-bit keys in the binning buffer (tests compare them)."""
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     if not means3D.is_cuda:
@@ -186,6 +188,7 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
     a.capacity = capacity
     a.num_rendered_pinned = sc.pinned_ptr
     a.ctrl_clean = 1
+    a.defer_count, a.write_keys = 0, int(bool(write_keys))
     sc.dirty.add("ctrl")  # until the call has returned without an exception
 
     n = sc.n_out

@@ -16,6 +16,16 @@ arm = B.Arm(impl, sc, grads, dev)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 pc = time.perf_counter
 marks = []
+inner = []
+if impl == "igs":
+    from instag_b200 import rasterizer as R0
+    _b = R0.binding()
+    class _Timed:  # the binding with rasterize() timed: what is left of Module() is Python
+        def __getattr__(self, k):
+            return getattr(_b, k)
+        def rasterize(self, *a):
+            t = pc(); r = _b.rasterize(*a); inner.append(pc() - t); return r
+    R0._host_binding = _Timed()
 def step():
     t = [pc()]
     k = arm.cur
@@ -42,7 +52,10 @@ def step():
     marks.append(t)
 for _ in range(30):
     flush.zero_(); step()
-torch.cuda.synchronize(); marks.clear()
+torch.cuda.synchronize(); marks.clear(); inner.clear()
+if impl == "igs":
+    from instag_b200 import rasterizer as R
+    R.binding().host_trace()
 ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(300)]
 t0 = pc()
 for s, e in ev:
@@ -55,6 +68,12 @@ names = ["prologue", "Module() incl. poll", "cat+dot", "backward()", "epilogue"]
 print(impl, "host us per phase (median):", {n: round(float(np.median(d[:, i])), 1) for i, n in enumerate(names)})
 print("host loop per step us:", round((t1 - t0) / 300 * 1e6, 1), " between steps (flush, events):",
       round(float(np.median(m[1:, 0] - m[:-1, -1])), 1))
+if impl == "igs":
+    print("binding.rasterize() us (median):", round(float(np.median(inner)) * 1e6, 1))
+    tr = R.binding().host_trace()
+    print("inside the node, host us: forward {alloc, args, igs_forward, autograd}:", [round(x, 1) for x in tr[:4]],
+          " backward {saved+count, alloc+args, igs_backward, views}:", [round(x, 1) for x in tr[4:8]],
+          " forwards {waited, deferred, count read in backward, recorded}:", [int(x) for x in tr[8:]])
 print("gpu us per step:", round(float(np.mean([s.elapsed_time(e) for s, e in ev])) * 1e3, 1))
 # no flush: can the host keep the GPU fed?
 torch.cuda.synchronize(); t0 = pc()

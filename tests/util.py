@@ -82,10 +82,6 @@ def igs_intermediates(P, H, W, num_rendered, geom, binb, img):
         ranges=img[il["ranges"]:il["ranges"] + 8 * T].view(torch.int32).view(T, 2),
         n_contrib=img[il["n_contrib"]:il["n_contrib"] + 4 * H * W].view(torch.int32),
         point_list=binb[bl["point_list"]:bl["point_list"] + 4 * num_rendered].view(torch.int32))
-    # keys start after the capacity-sized point_list: recover capacity from the buffer size
-    cap_guess = None
-    for cap in range(max(num_rendered, 1), max(num_rendered, 1) + 1):
-        cap_guess = cap
     out["_bin"] = binb
     return out
 
@@ -138,10 +134,15 @@ def run_igs(sc, grads=None, debug=False):
     from instag_b200 import rasterizer as R
     tsc = to_torch(sc)
     P, H, W = tsc["means3D"].shape[0], sc["H"], sc["W"]
-    n, color, depth, norm, alpha, radii, extra, geom, binb, img = R._forward_native(*raw_args_fwd(tsc, debug))
+    n, color, depth, norm, alpha, radii, extra, geom, binb, img = R._forward_native(*raw_args_fwd(tsc, debug),
+                                                                                   write_keys=True)
     torch.cuda.synchronize()
     out = dict(num_rendered=n, color=color, depth=depth, norm=norm, alpha=alpha, radii=radii, extra=extra)
     if P > 0:
+        # the reference's point_offsets is not on this library's path: produced on request
+        from instag_b200 import _native as N
+        N.check(N.lib().igs_point_offsets(P, geom.data_ptr(), torch.cuda.current_stream().cuda_stream), "point_offsets")
+        torch.cuda.synchronize()
         inter = igs_intermediates(P, H, W, n, geom, binb, img)
         inter.pop("_bin")
         cap = bin_capacity_from_bytes(binb.numel())

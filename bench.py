@@ -39,6 +39,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-synth", action="store_true", help="skip the auxiliary forward-only synthesis fps")
+    ap.add_argument("--value-only", action="store_true", help="kernel experiments: device-resident timing and stages only")
     ap.add_argument("--cloud", default=None, help="a GaussianModel .ply (save_ply format) to rasterize instead of the "
                                                    "synthetic cloud of --workload (image size and camera stay)")
     return ap.parse_args()
@@ -392,7 +393,7 @@ def main():
     value = eff_world * 1000.0 / ms
 
     # ---- end to end (host buffers, H2D + D2H inside the timed region) ----
-    if backward:
+    if backward and not a.value_only:
         ms_e2e, _, _ = timed(torch, dist, step_e2e, a.steps, max(a.warmup, 3), flush, eff_world)
         e2e = {"value": eff_world * 1000.0 / ms_e2e, "unit": "frames/s", "h2d_bytes_per_step": arm.h2d_bytes,
                "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e,

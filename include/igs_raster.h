@@ -214,14 +214,15 @@ int igs_point_offsets(int32_t P, void* geom, igs_stream_t stream);
 
 int igs_backward(const IgsBwdArgs* args, igs_stream_t stream);
 
-/* Measurement hooks (no reference counterpart; SURVEY.md 5 "tracing").  With
- * profiling enabled the library records CUDA events on the launching stream at
- * the stage boundaries of every igs_forward / igs_backward of this host
- * thread (a ring of the last 256 frames); igs_profile_read waits for them and
- * returns the MEAN stage durations in ms over the *frames recorded since
- * igs_profile_enable(1) (-1 = stage did not run): 0 preprocess+scan, 1 duplicate (+ the 4-byte
- * num_rendered copy), 2 per-tile depth sort, 3 (unused: the tile ranges come out of stage 0), 4 render,
- * 5 render backward, 6 per-Gaussian backward.  igs_launch_count returns how
+/* Measurement hooks (no reference counterpart; SURVEY.md 5 "tracing").  With profiling enabled
+ * the kernels of every igs_forward / igs_backward of this host thread leave device-side time stamps
+ * (%globaltimer of each kernel's last CTA; a ring of the last 256 frames), which costs one atomic per
+ * CTA and puts nothing between the kernels -- their programmatic dependent launches stay as they are.
+ * igs_profile_read synchronises the device and returns the MEAN stage durations in ms over the frames
+ * recorded since igs_profile_enable(1) (-1 = stage did not run).  A stage lasts from the completion of
+ * its predecessor to its own completion, so the stages of a half add up to the half: 0 preprocess (from
+ * its first CTA's start), 1 duplicate + tile ranges, 2 per-tile depth sort, 3 (unused), 4 render,
+ * 5 render backward (from its first CTA's start), 6 per-Gaussian backward.  igs_launch_count returns how
  * many kernels this host thread has launched through the library so far. */
 #define IGS_NUM_STAGES 7
 int igs_profile_enable(int on);

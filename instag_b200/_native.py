@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libigs_raster.so")
+# IGS_LIB: another build of the library (kernel experiments, profiles/tools); the default is the in-tree one
+LIB_PATH = os.environ.get("IGS_LIB") or os.path.join(_HERE, "libigs_raster.so")
 
 IGS_OK, IGS_ERR_INVALID, IGS_ERR_CUDA, IGS_ERR_CAPACITY = 0, -1, -2, -3
 MAX_EXTRA_DIMS = 34

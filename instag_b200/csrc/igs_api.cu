@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <initializer_list>
 #include "igs_common.cuh"
 #include "igs_kernels.cuh"
@@ -33,30 +34,35 @@ int stage_check(bool debug, cudaStream_t s, const char* what) {
   return check_cuda(e, what);
 }
 
-// ---- profiling: CUDA events on the launching stream, only when enabled -------
+// ---- profiling: device-side time stamps (igs_common.cuh "Prof"), only when enabled -------
 constexpr int PROF_RING = 256; // frames kept; older ones are overwritten
+static __device__ unsigned long long g_stamps[PROF_RING * ST_WORDS];
 struct Profiler {
   bool enabled = false;
-  int slot = -1;        // frame being recorded (advanced at boundary 0)
+  int slot = -1;        // frame being recorded (advanced by every forward)
   long long frames = 0; // frames started since enable
-  bool have[PROF_RING][PROF_BOUNDARIES] = {};
-  cudaEvent_t ev[PROF_RING][PROF_BOUNDARIES] = {};
+  unsigned long long* base = nullptr;
 };
 static thread_local Profiler g_prof;
 static thread_local unsigned long long g_launches = 0;
 
-void prof_mark(int b, cudaStream_t s) {
+Prof prof_begin(bool forward, cudaStream_t s) {
+  // IGS_PDL_EARLY=1: griddepcontrol.launch_dependents at the top of every kernel.  Off: measured on
+  // B200, dependents that take their places early slow their predecessors (C2 frame 222 -> 239 us)
+  static const int early = getenv("IGS_PDL_EARLY") && getenv("IGS_PDL_EARLY")[0] == '1';
+  Prof pr{nullptr, early};
   Profiler& p = g_prof;
-  if (!p.enabled) return;
-  if (b == 0) {
+  if (!p.enabled || !p.base) return pr;
+  if (forward) {
     p.slot = (p.slot + 1) % PROF_RING;
     p.frames++;
-    for (int k = 0; k < PROF_BOUNDARIES; k++) p.have[p.slot][k] = false;
+    if (cudaMemsetAsync(p.base + (size_t)p.slot * ST_WORDS, 0, ST_WORDS * sizeof(unsigned long long), s) != cudaSuccess) {
+      cudaGetLastError();
+      return pr;
+    }
   }
-  if (p.slot < 0) return;
-  cudaEvent_t& e = p.ev[p.slot][b];
-  if (!e) cudaEventCreate(&e);
-  p.have[p.slot][b] = cudaEventRecord(e, s) == cudaSuccess;
+  if (p.slot >= 0) pr.stamps = p.base + (size_t)p.slot * ST_WORDS;
+  return pr;
 }
 void count_launch(int n) { g_launches += (unsigned long long)n; }
 
@@ -174,15 +180,17 @@ static BinArgs make_bin(const IgsFwdArgs* a) {
   return ba;
 }
 
-static int run_bin_render(const IgsFwdArgs* a, cudaStream_t s) {
+static int run_bin_render(const IgsFwdArgs* a, cudaStream_t s, const Prof& prof) {
   const ImgLayout il(a->W, a->H);
   char* im = (char*)a->img;
   const bool debug = a->debug != 0;
-  const BinArgs ba = make_bin(a);
+  BinArgs ba = make_bin(a);
+  ba.prof = prof;
   if (int r = check_cuda(launch_binning(ba, s), "binning launch")) return r;
   if (int r = stage_check(debug, s, "binning (duplicate/tile sort)")) return r;
 
   RenderArgs ra{};
+  ra.prof = prof;
   ra.W = a->W; ra.H = a->H; ra.ED = a->ED; ra.grid_x = ba.grid_x; ra.grid_y = ba.grid_y;
   ra.header = ba.header;
   ra.ranges = ba.ranges;
@@ -197,7 +205,6 @@ static int run_bin_render(const IgsFwdArgs* a, cudaStream_t s) {
   ra.norm_len = (float*)(im + il.norm_len);
   ra.normalize = a->normalize_norm != 0;
   if (int r = check_cuda(launch_render(ra, s), "render launch")) return r;
-  prof_mark(5, s);
   return stage_check(debug, s, "render");
 }
 
@@ -252,16 +259,16 @@ int igs_forward(const IgsFwdArgs* a, igs_stream_t stream, int64_t* num_rendered)
     *a->num_rendered_pinned = 0;
     return stage_check(debug, s, "empty forward");
   }
-  const PreArgs pa = make_pre(a);
+  PreArgs pa = make_pre(a);
+  const Prof prof = prof_begin(true, s);
+  pa.prof = prof;
   int32_t* const slot_dev = device_view_of_pinned(a->num_rendered_pinned);
   volatile int32_t* const slot = (volatile int32_t*)a->num_rendered_pinned;
   if (slot_dev) *slot = -1; // the duplicate kernel's service CTA posts the count here (device-mapped pinned memory)
-  prof_mark(0, s);
   if (int r = check_cuda(launch_preprocess(pa, s), "preprocess launch")) return r;
-  prof_mark(1, s);
   if (int r = stage_check(debug, s, "preprocess")) return r;
   // speculative second half: sized by capacity, bounded on the device by num_rendered
-  if (int r = run_bin_render(a, s)) return r;
+  if (int r = run_bin_render(a, s, prof)) return r;
   if (a->defer_count && slot_dev) {
     // the caller reads the posted count later (igs_forward_count, or the slot itself: -1 = not
     // there yet) and holds it against the capacity; everything is queued, nothing on the device
@@ -352,7 +359,9 @@ int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
   if (!a->accum_clean)
     if (int r = check_cuda(cudaMemsetAsync(a->accum, 0, accum_bytes(a->P, a->ED), s), "memset accum")) return r;
 
+  const Prof prof = prof_begin(false, s);
   BwdRenderArgs ra{};
+  ra.prof = prof;
   ra.W = a->W; ra.H = a->H; ra.ED = a->ED;
   ra.grid_x = (a->W + TILE - 1) / TILE; ra.grid_y = (a->H + TILE - 1) / TILE;
   ra.ranges = (const uint2*)(im + il.ranges);
@@ -370,13 +379,12 @@ int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
   ra.accum = (float*)a->accum;
   ra.ticket = (uint32_t*)((char*)a->accum + accum_ticket_offset(a->P, a->ED));
   ra.accum_extra = a->ED > 1 ? (float*)((char*)a->accum + align_up((size_t)a->P * ACC_F * sizeof(float))) : nullptr;
-  prof_mark(6, s);
   if (a->num_rendered != 0) // (< 0: the caller does not know the count; the kernel finds empty lists by itself)
     if (int r = check_cuda(launch_render_backward(ra, s), "render backward launch")) return r;
-  prof_mark(7, s);
   if (int r = stage_check(debug, s, "render backward")) return r;
 
   BwdPreArgs pa{};
+  pa.prof = prof;
   pa.P = a->P; pa.D = a->D; pa.M = a->M; pa.ED = a->ED; pa.W = a->W; pa.H = a->H;
   pa.tan_fovx = a->tan_fovx; pa.tan_fovy = a->tan_fovy;
   pa.focal_y = a->H / (2.0f * a->tan_fovy); pa.focal_x = a->W / (2.0f * a->tan_fovx);
@@ -393,37 +401,52 @@ int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
   pa.dL_dsh = a->dL_dsh; pa.dL_dscales = a->dL_dscales; pa.dL_drotations = a->dL_drotations;
   pa.dL_dextra_attrs = a->dL_dextra_attrs;
   if (int r = check_cuda(launch_preprocess_backward(pa, s), "preprocess backward launch")) return r;
-  prof_mark(8, s);
   return stage_check(debug, s, "preprocess backward");
 }
 
 int igs_profile_enable(int on) {
   Profiler& p = g_prof;
+  if (on && !p.base) {
+    void* sym = nullptr;
+    if (int r = check_cuda(cudaGetSymbolAddress(&sym, g_stamps), "profile stamps")) return r;
+    p.base = (unsigned long long*)sym;
+  }
   p.enabled = on != 0;
   p.slot = -1;
   p.frames = 0;
-  for (int f = 0; f < PROF_RING; f++)
-    for (int k = 0; k < PROF_BOUNDARIES; k++) p.have[f][k] = false;
+  if (on)
+    if (int r = check_cuda(cudaMemset(p.base, 0, sizeof(unsigned long long) * PROF_RING * ST_WORDS), "profile reset")) return r;
   return IGS_OK;
 }
 
 int igs_profile_read(float* ms, int32_t* frames) {
   if (!ms) { set_error("null ms"); return IGS_ERR_INVALID; }
   Profiler& p = g_prof;
-  // stage k = boundary k -> k+1, except 5->6 (between forward and backward)
-  static const int from[IGS_NUM_STAGES] = {0, 1, 2, 3, 4, 6, 7};
+  for (int k = 0; k < IGS_NUM_STAGES; k++) ms[k] = -1.f;
+  if (frames) *frames = 0;
+  if (!p.base) return IGS_OK;
+  if (int r = check_cuda(cudaDeviceSynchronize(), "profile sync")) return r;
+  static thread_local unsigned long long host[PROF_RING * ST_WORDS];
+  if (int r = check_cuda(cudaMemcpy(host, p.base, sizeof host, cudaMemcpyDeviceToHost), "profile read")) return r;
+  // stage k: from stamp `from` (its predecessor's last CTA; inverted = a start stamp) to stamp `to`
+  static const int to[IGS_NUM_STAGES] = {ST_PRE, ST_DUP, ST_SORT, -1, ST_RENDER, ST_RBWD, ST_PBWD};
+  static const int from[IGS_NUM_STAGES] = {ST_FWD_START, ST_PRE, ST_DUP, -1, ST_SORT, ST_BWD_START, ST_RBWD};
   int used = 0;
   for (int k = 0; k < IGS_NUM_STAGES; k++) {
+    if (to[k] < 0) continue;
     double sum = 0.0;
     int n = 0;
-    const int a = from[k], b = a + 1;
-    for (int f = 0; f < PROF_RING; f++) {
-      if (!p.have[f][a] || !p.have[f][b]) continue;
-      if (int r = check_cuda(cudaEventSynchronize(p.ev[f][b]), "profile sync")) return r;
-      float t = 0.f;
-      if (cudaEventElapsedTime(&t, p.ev[f][a], p.ev[f][b]) == cudaSuccess) { sum += t; n++; }
+    const int recorded = (int)(p.frames < PROF_RING ? p.frames : PROF_RING);
+    for (int f = 0; f < recorded; f++) {
+      const unsigned long long* st = host + (size_t)f * ST_WORDS;
+      unsigned long long t0 = st[from[k]], t1 = st[to[k]];
+      if (!t0 || !t1) continue;
+      if (from[k] == ST_FWD_START || from[k] == ST_BWD_START) t0 = ~t0;
+      if (t1 < t0) continue;
+      sum += (double)(t1 - t0) * 1e-6;
+      n++;
     }
-    ms[k] = n ? (float)(sum / n) : -1.f;
+    if (n) ms[k] = (float)(sum / n);
     if (n > used) used = n;
   }
   if (frames) *frames = used;

@@ -157,7 +157,7 @@ __device__ void tile_service(const BinArgs& a, const bool abs_cursors) {
 }
 
 __global__ void __launch_bounds__(DUP_THREADS) tile_scan_kernel(BinArgs a) {
-  pdl_launch_dependents();
+  if (a.prof.early) pdl_launch_dependents();
   pdl_wait();
   tile_service(a, true);
 }
@@ -174,11 +174,15 @@ __global__ void __launch_bounds__(DUP_THREADS) duplicate_kernel(BinArgs a) {
   __shared__ uint32_t s_scan[DUP_WARPS];
   const int tid = threadIdx.x, lane = tid & 31;
   const int T = a.num_tiles;
-  pdl_launch_dependents();
+  if (a.prof.early) pdl_launch_dependents();
   if (HIST_SMEM && blockIdx.x != 0)
     for (int t = tid; t < T; t += DUP_THREADS) s_slot[t] = 0u;
   pdl_wait(); // everything below reads what the preprocess kernel wrote
-  if (HIST_SMEM && blockIdx.x == 0) { tile_service(a, false); return; }
+  if (HIST_SMEM && blockIdx.x == 0) {
+    tile_service(a, false);
+    if (tid == 0) stamp_done(a.prof, ST_DUP);
+    return;
+  }
   const int g = (int)(blockIdx.x - (HIST_SMEM ? 1 : 0)) * DUP_THREADS + tid;
   uint32_t n = 0, xy = 0, w = 1, depth = 0;
   if (g < a.P) n = __ldg(a.tiles_touched + g);
@@ -234,11 +238,13 @@ __global__ void __launch_bounds__(DUP_THREADS) duplicate_kernel(BinArgs a) {
     for_each_instance(n, xy, w, depth, gbase, a.grid_x, [&](uint32_t t, unsigned long long word) {
       a.pairs[atomicAdd(&s_slot[t], 1u)] = word;
     });
+    if (tid == 0) stamp_done(a.prof, ST_DUP);
   } else {
     if (__ldcg(&a.header->overflow)) return; // (written by tile_scan_kernel, which ran before this grid)
     for_each_instance(n, xy, w, depth, gbase, a.grid_x, [&](uint32_t t, unsigned long long word) {
       a.pairs[atomicAdd(a.tile_cursor + (size_t)t * CNT_STRIDE, 1u)] = word; // absolute cursors
     });
+    if (tid == 0) stamp_done(a.prof, ST_DUP);
   }
 }
 
@@ -427,7 +433,7 @@ __device__ void sort_segment_big(TileSortShared& sh, const unsigned long long* _
 __global__ void __launch_bounds__(TS_THREADS) tile_sort_kernel(BinArgs a) {
   __shared__ TileSortShared sh;
   const int tile = blockIdx.x;
-  pdl_launch_dependents();
+  if (a.prof.early) pdl_launch_dependents();
   pdl_wait(); // the duplicate kernel's segments and tile ranges
   const uint2 range = a.ranges[tile];
   const int n = (int)(range.y - range.x);
@@ -442,6 +448,7 @@ __global__ void __launch_bounds__(TS_THREADS) tile_sort_kernel(BinArgs a) {
   uint64_t* out_key = a.keys ? a.keys + range.x : nullptr;
   if (n <= TS_CAP) sort_segment(sh, a.pairs + range.x, n, out_id, out_key, tile_hi);
   else sort_segment_big(sh, a.pairs + range.x, a.pairs2 + range.x, n, out_id, out_key, tile_hi);
+  if (threadIdx.x == 0) stamp_done(a.prof, ST_SORT);
 }
 
 // The reference's point_offsets (inclusive prefix sum of tiles_touched, rasterizer_impl.cu:280),
@@ -488,10 +495,7 @@ cudaError_t launch_binning(const BinArgs& a, cudaStream_t s) {
     if (e == cudaSuccess) e = launch_after(duplicate_kernel<false>, dim3(dup_blocks), dim3(DUP_THREADS), 0, s, a);
     count_launch(2);
   }
-  prof_mark(2, s);
   if (e == cudaSuccess) e = launch_after(tile_sort_kernel, dim3(a.num_tiles), dim3(TS_THREADS), 0, s, a);
-  prof_mark(3, s);
-  prof_mark(4, s);
   count_launch();
   return e;
 }

@@ -133,12 +133,18 @@ void set_error(const char* fmt, ...);
 int check_cuda(cudaError_t e, const char* what);
 int stage_check(bool debug, cudaStream_t s, const char* what);
 
-// optional per-stage timing + launch accounting (igs_api.cu; include/igs_raster.h
-// igs_profile_*).  Boundaries: 0 fwd start | 1 preprocess done | 2 duplicate done |
-// 3 sort done | 4 ranges done | 5 render done | 6 bwd start | 7 render-backward done |
-// 8 per-Gaussian backward done.
-constexpr int PROF_BOUNDARIES = 9;
-void prof_mark(int boundary, cudaStream_t s);
+// optional per-stage timing + launch accounting (igs_api.cu; include/igs_raster.h igs_profile_*).
+// The kernels of a frame overlap their launches (programmatic dependent launch), so stage times are
+// taken ON THE DEVICE: with profiling on, every CTA leaves %globaltimer in the frame's stamp block
+// when it is done (atomicMax), and the first kernel of each half leaves the earliest time at which
+// one of its CTAs got past griddepcontrol.wait.  A stage = from its predecessor's last CTA to its
+// own last CTA; the stages of a half add up to the half.  Nothing sits between the kernels.
+enum : int { ST_FWD_START = 0, ST_PRE, ST_DUP, ST_SORT, ST_RENDER, ST_BWD_START, ST_RBWD, ST_PBWD, ST_WORDS = 16 };
+struct Prof {
+  unsigned long long* stamps; // [ST_WORDS] of this frame, zeroed when the frame starts; NULL: not profiling
+  int early;                  // != 0: release the programmatic dependents at the top of the kernel
+};
+Prof prof_begin(bool forward, cudaStream_t s); // advances to the next frame's block when forward
 void count_launch(int n = 1);
 
 // ---- programmatic dependent launch ------------------------------------------------
@@ -155,6 +161,14 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 // clears, constant loads) on whatever SM resources are free and then block in pdl_wait() until
 // this grid has completed.  Without it they are only scheduled as this grid's CTAs exit.
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// (one thread per CTA / per warp calls these)
+__device__ __forceinline__ void stamp_done(const Prof& p, int word) { if (p.stamps) atomicMax(p.stamps + word, global_ns()); }
+__device__ __forceinline__ void stamp_begun(const Prof& p, int word) { if (p.stamps) atomicMax(p.stamps + word, ~global_ns()); }
 
 template <class... KArgs, class... Args>
 inline cudaError_t launch_after(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,

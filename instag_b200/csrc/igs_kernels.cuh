@@ -5,6 +5,7 @@
 namespace igs {
 
 struct PreArgs {
+  Prof prof;
   int P, D, M, ED, W, H, grid_x, grid_y, prefiltered;
   float tan_fovx, tan_fovy, focal_x, focal_y, scale_modifier;
   int64_t capacity;
@@ -19,6 +20,7 @@ struct PreArgs {
 };
 
 struct BinArgs {
+  Prof prof;
   int P, grid_x, grid_y, num_tiles;
   int64_t capacity;
   const int32_t* radii;
@@ -39,6 +41,7 @@ struct BinArgs {
 };
 
 struct RenderArgs {
+  Prof prof;
   int W, H, ED, grid_x, grid_y;
   CtrlHeader* header; // overflow flag: the tile lists are incomplete, render nothing; unit ticket
   const uint2* ranges;
@@ -54,6 +57,7 @@ struct RenderArgs {
 };
 
 struct BwdRenderArgs {
+  Prof prof;
   int W, H, ED, grid_x, grid_y;
   const uint2* ranges;
   const uint32_t* tile_order;
@@ -73,6 +77,7 @@ struct BwdRenderArgs {
 };
 
 struct BwdPreArgs {
+  Prof prof;
   int P, D, M, ED, W, H;
   float tan_fovx, tan_fovy, focal_x, focal_y, scale_modifier;
   const float *viewmatrix, *projmatrix, *campos;

@@ -88,10 +88,11 @@ __global__ void __launch_bounds__(PRE_THREADS, 1024 / PRE_THREADS) preprocess_ke
   extern __shared__ uint32_t s_hist[];
   const int tid = threadIdx.x;
   const int T = a.grid_x * a.grid_y;
-  pdl_launch_dependents(); // the duplicate kernel's CTAs may take their places (they wait for this grid to finish)
+  if (a.prof.early) pdl_launch_dependents(); // the duplicate kernel's CTAs may take their places (they wait for this grid to finish)
   if (HIST_SMEM)
     for (int t = tid; t < T; t += PRE_THREADS) s_hist[t] = 0u;
   pdl_wait(); // launched as a programmatic dependent of whatever precedes it on the stream
+  if (tid == 0) stamp_begun(a.prof, ST_FWD_START);
   if (tid < 16) { s_view[tid] = __ldg(a.viewmatrix + tid); s_proj[tid] = __ldg(a.projmatrix + tid); }
   if (tid < 3) s_cam[tid] = __ldg(a.campos + tid);
   __syncthreads();
@@ -193,6 +194,7 @@ __global__ void __launch_bounds__(PRE_THREADS, 1024 / PRE_THREADS) preprocess_ke
       if (c) atomicAdd(a.tile_count + (size_t)t * CNT_STRIDE, c);
     }
   }
+  if (tid == 0) stamp_done(a.prof, ST_PRE);
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,

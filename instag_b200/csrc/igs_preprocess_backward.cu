@@ -129,7 +129,7 @@ template <bool USE_SH>
 __global__ void __launch_bounds__(256) preprocess_backward_kernel(BwdPreArgs a) {
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   const int tid = threadIdx.x;
-  pdl_launch_dependents();
+  if (a.prof.early) pdl_launch_dependents();
   if (tid < 16) { s_view[tid] = __ldg(a.viewmatrix + tid); s_proj[tid] = __ldg(a.projmatrix + tid); }
   if (tid < 3) s_cam[tid] = __ldg(a.campos + tid);
   pdl_wait(); // the accumulator rows of the render-backward kernel
@@ -322,6 +322,7 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(BwdPreArgs a) 
 #pragma unroll
   for (int k = 0; k < 6; k++) a.dL_dcov3D[6 * idx + k] = dcov[k];
   reinterpret_cast<float4*>(a.dL_drotations)[idx] = drot;
+  if (tid == 0) stamp_done(a.prof, ST_PBWD);
 }
 
 cudaError_t launch_preprocess_backward(const BwdPreArgs& a, cudaStream_t s) {

@@ -53,18 +53,32 @@ __device__ __forceinline__ float4 lds128(uint32_t addr) {
 __device__ __forceinline__ void sts128(uint32_t addr, float4 v) {
   asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
+// 16 bytes global -> shared without a register in between (LDGSTS): the copy is in flight while the warp works
+__device__ __forceinline__ void copy16_async(uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void copies_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void copies_wait() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 
 // Persistent kernel: every SM holds as many 4-warp CTAs as fit, and every WARP pulls (tile,
 // 8x4 block) units from one global ticket, heaviest tiles first (tile_order), until the
 // frame is done -- the four sub-partitions of an SM stay evenly loaded to the end.
 template <int ED_T> // 0, 1, or -1 = generic (runtime ED up to IGS_MAX_EXTRA_DIMS)
-__global__ void __launch_bounds__(RT) render_kernel(RenderArgs a) {
-  // per warp: 4 planes of 32 float4 (r0..r3 of the chunk's survivors) = 2 KB
-  __shared__ float4 s_rec[RW][4][32];
+__global__ void __launch_bounds__(RT, 6) render_kernel(RenderArgs a) {
+  // per warp, 3 KB: planes r0, r1 of the chunk's survivors (stored by the survivors after the cull,
+  // from the registers the cull data was prefetched into), and, double buffered, planes r2, r3 of
+  // EVERY entry of the chunk, copied in asynchronously one chunk ahead (cp.async: no register in
+  // between).  A survivor's colour / normal are then in shared memory when its first blend needs them:
+  // fetched after the cull, that load was the kernel's largest single stall (11 % of the samples).
+  // (Measured and dropped: all four planes through a cp.async ring two chunks ahead -- 66.0 us against
+  // 63.7; 7 / 8 resident CTAs per SM at 64 registers -- 72.0 / 77.7 us: the kernel is issue bound while
+  // its warps are busy, more of them only stretch the heavy units that make the tail.)
+  __shared__ float4 s_rec[RW][6][32];
   __shared__ uint32_t s_id[ED_T < 0 ? RW : 1][32];
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  pdl_launch_dependents();
+  if (a.prof.early) pdl_launch_dependents();
   pdl_wait(); // the sorted tile lists
   if (a.header->overflow) return;
   const int num_units = a.grid_x * a.grid_y * 8;
@@ -106,15 +120,22 @@ __global__ void __launch_bounds__(RT) render_kernel(RenderArgs a) {
   uint32_t last_contributor = 0;
   bool done = !inside;
 
-  // software pipeline: ids two chunks ahead, cull data (r0, r1) one chunk ahead
+  // software pipeline: ids two chunks ahead, cull data (r0, r1: registers) and colour / normal planes
+  // (r2, r3: shared memory) one chunk ahead.  The two r2 / r3 buffers sit behind the r0 / r1 planes:
+  // r2 plane at +1024 (+2048), r3 plane 512 further.
   uint32_t id_cur = 0, id_nxt = 0;
   float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f), q1 = q0;
   if (lane < total) id_cur = __ldg(list + lane);
   if (32 + lane < total) id_nxt = __ldg(list + 32 + lane);
   if (lane < total) {
-    q0 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4);
-    q1 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4 + 1);
+    const float4* rec = a.splat + (size_t)id_cur * SPLAT_F4;
+    q0 = __ldg(rec);
+    q1 = __ldg(rec + 1);
+    copy16_async(smine + 1024, rec + 2);
+    copy16_async(smine + 1536, rec + 3);
   }
+  copies_commit();
+  uint32_t par = 0; // which r2 / r3 buffer the current chunk reads
 
   for (int cb = 0; cb < total; cb += 32) {
     if (__all_sync(0xffffffffu, done)) break;
@@ -125,22 +146,26 @@ __global__ void __launch_bounds__(RT) render_kernel(RenderArgs a) {
     unsigned m = __ballot_sync(0xffffffffu, hit);
     const uint32_t id_mine = id_cur;
     const float4 c0 = q0, c1 = q1;
-    // prefetch the next chunk's cull data and the ids of the chunk after it
+    // this chunk's r2 / r3 planes have landed; everybody is done reading the previous chunk's slots
+    copies_wait();
+    __syncwarp();
+    // prefetch the next chunk's cull data and colour / normal planes, and the ids of the chunk after it
     id_cur = id_nxt;
+    const uint32_t cur = sbase + 1024 + par * 1024; // r2 plane of this chunk (r3: +512)
+    par ^= 1u;
     if (cb + 32 + lane < total) {
-      q0 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4);
-      q1 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4 + 1);
+      const float4* rec = a.splat + (size_t)id_cur * SPLAT_F4;
+      q0 = __ldg(rec);
+      q1 = __ldg(rec + 1);
+      copy16_async(smine + 1024 + par * 1024, rec + 2);
+      copy16_async(smine + 1536 + par * 1024, rec + 3);
     }
+    copies_commit();
     if (cb + 64 + lane < total) id_nxt = __ldg(list + cb + 64 + lane);
     if (m == 0) continue;
-    __syncwarp(); // everybody is done reading the previous chunk's slots
     if (hit) {
-      const float4* rec = a.splat + (size_t)id_mine * SPLAT_F4;
-      const float4 c2 = __ldg(rec + 2), c3 = __ldg(rec + 3);
       sts128(smine, c0);
       sts128(smine + 512, c1);
-      sts128(smine + 1024, c2);
-      sts128(smine + 1536, c3);
       if (ED_T < 0) s_id[warp][lane] = id_mine;
     }
     __syncwarp();
@@ -188,8 +213,8 @@ __global__ void __launch_bounds__(RT) render_kernel(RenderArgs a) {
       // (forward.cu:425-431), far inside the 1e-5 image tolerance
 #pragma unroll
       for (int h = 0; h < RG; h++) {
-        const float4 r2 = lds128(sbase + 1024 + j[h] * 16);
-        const float4 r3 = lds128(sbase + 1536 + j[h] * 16);
+        const float4 r2 = lds128(cur + j[h] * 16);
+        const float4 r3 = lds128(cur + 512 + j[h] * 16);
         C0 = __fmaf_rn(r2.x, w[h], C0);
         C1 = __fmaf_rn(r2.y, w[h], C1);
         C2 = __fmaf_rn(r2.z, w[h], C2);
@@ -229,12 +254,14 @@ __global__ void __launch_bounds__(RT) render_kernel(RenderArgs a) {
     if (ED_T < 0)
       for (int c = 0; c < ED; c++) a.out_extra[c * HW + pix] = Ex[c];
   }
-  __syncwarp(); // the next unit reuses this warp's shared-memory slots
+  copies_wait(); // (a unit that stopped early leaves its last prefetch in flight)
+  __syncwarp();  // the next unit reuses this warp's shared-memory slots
   if (trace && lane == 0) {
     trace[3 * unit] = t_start; trace[3 * unit + 1] = gtimer();
     trace[3 * unit + 2] = (unsigned long long)smid() | ((unsigned long long)total << 32);
   }
  } // unit loop
+  if (lane == 0) stamp_done(a.prof, ST_RENDER);
 }
 
 // CTAs that fit on the device at once (all SMs), per kernel variant; cached per process
@@ -244,10 +271,11 @@ static int resident_ctas(K kernel, int threads) {
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0);
-  // 6 x 4 warps per SM measured best on B200 (sweep 2..8 in profiles/r01_v3_notes.md): fewer
-  // resident warps leave a deeper ticket queue (better balance), more hide more latency
-  per_sm = min(per_sm, 6);
-  if (const char* e = getenv("IGS_CTAS_PER_SM")) per_sm = max(1, atoi(e)); // experiments only
+  // 5 x 4 warps per SM measured best on B200 (4 / 5 / 6: 63.4 / 62.5 / 64.0 us, profiles/r02_notes.md):
+  // the kernel is issue bound while its warps are busy; fewer resident warps leave a deeper ticket
+  // queue and give the heavy units that make the tail a larger share of their scheduler
+  per_sm = min(per_sm, 5);
+  if (const char* e = getenv("IGS_FWD_CTAS")) per_sm = max(1, atoi(e)); // experiments only
   return (sms > 0 ? sms : 148) * (per_sm > 0 ? per_sm : 1);
 }
 

@@ -92,8 +92,9 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
   __shared__ float4 s_bm[2][32];
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  pdl_launch_dependents();
+  if (a.prof.early) pdl_launch_dependents();
   pdl_wait(); // whatever ran before on the stream (the forward, the caller's loss kernels) is complete
+  if (threadIdx.x == 0) stamp_begun(a.prof, ST_BWD_START);
   const int num_units = a.grid_x * a.grid_y * 8;
   const int ED = ED_T < 0 ? a.ED : ED_T;
   const size_t HW = (size_t)a.H * a.W;
@@ -369,6 +370,7 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
   if (pend_at & 511u) flush((int)(pend_at & 511u) >> 4);
   __syncwarp(); // the next unit reuses this warp's shared-memory slots
  } // unit loop
+  if (lane == 0) stamp_done(a.prof, ST_RBWD);
 }
 
 template <class K>
@@ -381,7 +383,7 @@ static int resident_ctas_bwd(K kernel, int threads) {
   // 6 x 4 warps per SM measured best on B200 (sweep 2..8 in profiles/r01_v3_notes.md): fewer
   // resident warps leave a deeper ticket queue (better balance), more hide more latency
   per_sm = min(per_sm, 6);
-  if (const char* e = getenv("IGS_CTAS_PER_SM")) per_sm = max(1, atoi(e)); // experiments only
+  if (const char* e = getenv("IGS_BWD_CTAS")) per_sm = max(1, atoi(e)); // experiments only
   return (sms > 0 ? sms : 148) * (per_sm > 0 ? per_sm : 1);
 }
 

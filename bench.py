@@ -35,11 +35,15 @@ def parse():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="igs", choices=["igs", "reference"])
-    ap.add_argument("--workload", default="C2", choices=["C2", "C3", "C3_face", "C3_mouth", "C1", "C5"])
+    ap.add_argument("--workload", default="C2", choices=["C2", "C3", "C3_face", "C3_mouth", "C1", "C5", "shell",
+                                                         "concentrated", "opacity_extreme", "pair"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-synth", action="store_true", help="skip the auxiliary forward-only synthesis fps")
     ap.add_argument("--value-only", action="store_true", help="kernel experiments: device-resident timing and stages only")
+    ap.add_argument("--no-graph", action="store_true", help="skip the CUDA-graph replay of the end-to-end step")
+    ap.add_argument("--no-c5", action="store_true", help="skip the BASELINE config-5 leg (8 views of 1M Gaussians dealt to the ranks)")
+    ap.add_argument("--no-adjacent", action="store_true", help="skip the throughput of the kernels either side of the path")
     ap.add_argument("--cloud", default=None, help="a GaussianModel .ply (save_ply format) to rasterize instead of the "
                                                    "synthetic cloud of --workload (image size and camera stay)")
     return ap.parse_args()
@@ -96,39 +100,73 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
-def ncu_traffic(stage):
-    """DRAM bytes per launch of `stage`'s kernel from the newest committed ncu --set full summary
-    (profiles/rNN_vN_full.md, written by profiles/summarize.py); None if there is none."""
+KERNEL_OF = {"preprocess": "preprocess_kernel", "duplicate": "duplicate_kernel", "sort": "tile_sort_kernel",
+             "render": "render_kernel", "render_backward": "render_backward_kernel",
+             "preprocess_backward": "preprocess_backward_kernel"}
+# which roof bounds which kernel: HBM for the per-Gaussian / binning kernels, FP32 instruction
+# issue for the two compositing kernels (nothing on the path is a dense contraction)
+BOUND_OF = {"preprocess": "hbm", "duplicate": "hbm", "sort": "hbm", "preprocess_backward": "hbm",
+            "render": "fp32_issue", "render_backward": "fp32_issue"}
+
+
+def ncu_metrics(stage, workload="C2"):
+    """Metrics of `stage`'s kernel from the newest committed ncu --set full summary of `workload`
+    (profiles/rNN_*_full[_C5].md, written by profiles/summarize.py): {metric: value}; {} if none."""
     import glob
     import re
-    kern = {"preprocess": "preprocess_kernel", "duplicate": "duplicate_kernel", "sort": "tile_sort_kernel",
-            "render": "render_kernel", "render_backward": "render_backward_kernel",
-            "preprocess_backward": "preprocess_backward_kernel"}.get(stage)
-    files = sorted(f for f in glob.glob(os.path.join(ROOT, "profiles", "r*_full.md")) if "_C5" not in f)
+    kern = KERNEL_OF.get(stage)
+    files = sorted(f for f in glob.glob(os.path.join(ROOT, "profiles", "r*_full*.md"))
+                   if ("_C5" in f) == (workload == "C5"))
     if not kern or not files:
-        return None
+        return {}
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-    total, inside = None, False
+    out, inside = {}, False
     for ln in open(files[-1]):
         if ln.startswith("###"):
             inside = kern + "<" in ln or kern + "(" in ln
+            if inside:
+                out = {"_file": os.path.basename(files[-1])}
         elif inside:
-            m = re.match(r"- dram__bytes_(read|write)\.sum: ([0-9.]+) (\w+)", ln)
+            m = re.match(r"- ([\w.]+): ([0-9.,]+) ?(\w*)", ln)
             if m:
-                total = (total or 0.0) + float(m.group(2)) * unit.get(m.group(3), 1.0)
-    return total
+                out[m.group(1)] = float(m.group(2).replace(",", "")) * unit.get(m.group(3), 1.0)
+    return out
+
+
+def ncu_traffic(stage, workload="C2"):
+    m = ncu_metrics(stage, workload)
+    if "dram__bytes_read.sum" not in m:
+        return None
+    return m["dram__bytes_read.sum"] + m.get("dram__bytes_write.sum", 0.0)
+
+
+def ncu_issue(stage, workload="C2"):
+    """Share of ALL issue slots of the kernel's duration that issued an instruction, from the ncu
+    summary: issue-active (% of the cycles in which the sub-partition had a warp) x the share of the
+    elapsed cycles in which it had one."""
+    m = ncu_metrics(stage, workload)
+    try:
+        act = m["smsp__issue_active.avg.pct_of_peak_sustained_active"] / 100.0
+        share = m["smsp__cycles_active.avg"] / m["sm__cycles_elapsed.max"]
+    except KeyError:
+        return None
+    return {"issue_active_while_active": act, "active_share_of_elapsed": share, "of_elapsed_issue_slots": act * share,
+            "fma_pipe_pct_while_active": m.get("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active"),
+            "warp_instructions": m.get("smsp__inst_executed.sum"), "source": m.get("_file")}
 
 
 def algorithmic_bytes(P, N, HW, T, S=0, c=0, ED=1):
-    """Per-stage algorithmic bytes with this library's record sizes (DESIGN.md "Kernels"):
-    preprocess reads 44(+12S) B and writes the 64 B splat record + radii/tiles/offsets (+1 clamp),
-    4 B of tile-count atomic per instance and the tile ranges; duplicate reads 24 B per Gaussian and
-    writes one 8 B word per instance (+ a 4 B cursor atomic); the tile sort reads the words and
-    writes point_list + keys; render reads 4+64 B per instance and writes the images."""
+    """Per-stage algorithmic bytes with this library's record sizes (DESIGN.md "Kernels"): what each
+    kernel has to move once.  preprocess reads 44(+12S) B per Gaussian and writes the 64 B splat record
+    + radii + tiles_touched (+1 clamp); duplicate reads 24 B per Gaussian and the T tile counts, writes
+    one 8 B word per instance, the tile ranges and the tile order; the tile sort reads the words and
+    writes point_list; render reads 4+64 B per instance and writes the images; render backward
+    reads the same + the upstream images and adds into the 64 B accumulator rows; the per-Gaussian
+    backward reads accumulator + record + inputs and writes every gradient."""
     return {
-        "preprocess": (44 + 12 * S + 64 + 12 + c) * P + 4 * N + 12 * T,
-        "duplicate": 24 * P + 12 * N,
-        "sort": 8 * N + 12 * N,
+        "preprocess": (44 + 12 * S + 64 + 8 + c) * P,
+        "duplicate": 24 * P + 8 * N + 16 * T,
+        "sort": 8 * N + 4 * N,
         "render": (4 + 64) * N + (4 * (8 + ED) + 4) * HW,
         "render_backward": (4 + 64) * N + (8 + 4 * (8 + ED)) * HW + 2 * 64 * P,
         "preprocess_backward": (64 + 64 + 44 + 12 * S + c + 4 * (26 + 3 * (S if S else 0) + ED)) * P,
@@ -155,11 +193,24 @@ class Arm:
             from instag_b200 import rasterizer as R
             from diff_gauss import GaussianRasterizer
             self.fwd_raw, self.bwd_raw, self.Module = R._forward_native, R._backward_native, GaussianRasterizer
+            settings_cls = None
         else:
-            from oracle import ref_cuda as RC
-            self.fwd_raw, self.bwd_raw, self.Module = RC.forward_raw, RC.backward_raw, RC.RefGaussianRasterizer
+            # the reference's OWN extension, unmodified: its Python module, its pybind / torch binding, its
+            # kernels (baseline/_ref, built by baseline/build_ref.sh); where that build is absent, its three
+            # kernel files behind this repo's C shim (oracle/_ref) -- the line says which
+            from baseline import reference as BR
+            if BR.available():
+                ref = BR.load()
+                self.fwd_raw, self.bwd_raw, self.Module = ref._C.rasterize_gaussians, ref._C.rasterize_gaussians_backward, ref.GaussianRasterizer
+                settings_cls = ref.GaussianRasterizationSettings
+                self.reference_host = "the reference's own extension (baseline/_ref: diff_gauss/__init__.py + rasterize_points.cu + ext.cpp + cuda_rasterizer/*, unmodified, sm_100a)"
+            else:
+                from oracle import ref_cuda as RC
+                self.fwd_raw, self.bwd_raw, self.Module = RC.forward_raw, RC.backward_raw, RC.RefGaussianRasterizer
+                settings_cls = None
+                self.reference_host = "the reference's three kernel files behind this repo's C shim (oracle/_ref/libdgr_ref.so)"
         self.fargs = U.raw_args_fwd(self.t)
-        self.rs = U.settings_from(self.t)
+        self.rs = U.settings_from(self.t, cls=settings_cls)
         # ---- end-to-end harness (identical for both arms) ----
         # one pinned host block holding this step's inputs back to back, copied with ONE H2D per step
         # into one of two device blocks on a copy stream (input prefetch, as a data loader does): the
@@ -231,6 +282,55 @@ class Arm:
         self.cur = k ^ 1
         return leaves, m2
 
+    # ---- the same step recorded into CUDA graphs (igs arm only: the reference's forward blocks on a
+    # cudaMemcpy of num_rendered, rasterizer_impl.cu:284, and cannot be recorded) ----
+    def build_graphs(self):
+        """Two graphs, one per input block: graph k = {H2D of the NEXT step's inputs into block k^1 on a
+        forked stream} || {GaussianRasterizer(...) on block k -> loss -> backward -> loss D2H}.  Recorded
+        through the public module API; a replay is one step with the same copies as step_e2e."""
+        torch = self.torch
+        side = torch.cuda.Stream(self.device)
+        self.graph_stream = side
+        self.graphs, self.graph_keep = [], []
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            for _ in range(3):  # warm-up on the recording stream: workspaces, capacity hints, autograd buffers
+                for k in (0, 1):
+                    self._graph_body(k, side)
+            side.synchronize()
+            for k in (0, 1):
+                for v in self.leaves[k].values():
+                    v.grad = None
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=side):
+                    self.graph_keep.append(self._graph_body(k, side))
+                self.graphs.append(g)
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        torch.cuda.synchronize()
+        self.cur = 0
+
+    def _graph_body(self, k, stream):
+        torch = self.torch
+        self.copy_stream.wait_stream(stream)  # fork: the next step's inputs travel under this step's kernels
+        with torch.cuda.stream(self.copy_stream):
+            self.dev[k ^ 1].copy_(self.host, non_blocking=True)
+        leaves = self.leaves[k]
+        m2 = torch.zeros_like(leaves["means3D"], requires_grad=True)
+        color, depth, norm, alpha, radii, extra = self.Module(self.rs)(
+            means3D=leaves["means3D"], means2D=m2, shs=leaves.get("shs"),
+            colors_precomp=leaves.get("colors_precomp"), opacities=leaves["opacities"], scales=leaves["scales"],
+            rotations=leaves["rotations"], extra_attrs=leaves.get("extra_attrs"))
+        outs = [color, depth, norm, alpha] + ([extra] if self.ED else [])
+        loss = torch.dot(torch.cat([o.reshape(-1) for o in outs]), self.wflat)
+        loss.backward()
+        self.loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+        stream.wait_stream(self.copy_stream)  # join
+        return leaves, m2, loss
+
+    def step_e2e_graph(self):
+        self.graphs[self.cur].replay()
+        self.cur ^= 1
+
 
 def timed(torch, dist, step, steps, warmup, flush, world):
     """W untimed + EXACTLY K timed steps; CUDA events per step on the current stream, L2 flushed
@@ -299,14 +399,16 @@ def main():
         return  # the reference arm is a single-GPU number: rank 0 alone runs it
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
-    if a.workload == "C3":  # a single-camera step: replicas only, rank 0 reports it
-        return c3_pair(a, torch, dist, device, local) if rank == 0 else None
+    if a.workload in ("C3", "pair"):  # a single-camera step: replicas only, rank 0 reports it
+        if rank != 0:
+            return None
+        return (c3_pair if a.workload == "C3" else face_pair)(a, torch, dist, device, local)
     if world > 1 and a.impl == "igs":
         dist.init_process_group("nccl", device_id=device)
     eff_world = world if a.impl == "igs" else 1
 
     cfg = dict(S.CONFIGS[a.workload])
-    cloud = S.make_cloud(cfg["P"], sh_degree=cfg["sh_degree"], M=cfg["M"] or None, seed=0)
+    cloud = S.cloud_for(cfg, seed=0)
     if a.cloud:
         cloud = cloud_from_ply(a.cloud)
         cfg["P"], cfg["sh_degree"], cfg["M"] = cloud["means3D"].shape[0], cloud["sh_degree"], cloud["shs"].shape[1]
@@ -321,7 +423,8 @@ def main():
 
     if a.impl == "reference":
         from oracle import ref_cuda
-        if not ref_cuda.available():
+        from baseline import reference as BR
+        if not BR.available() and not ref_cuda.available():
             return reference_cpu_arm(a, sc, grads, backward, cfg)
     arm = Arm(a.impl, sc, grads, device)
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=device)
@@ -341,6 +444,11 @@ def main():
                 collective = f"NCCL all-reduce (NVLS unavailable: {str(ex)[:80]})"
 
     a.collective = collective
+    a.collective_check = None
+    if block is not None:
+        a.collective_check = collective_check(torch, dist, block, device)
+        if not (a.collective_check["bit_identical"] or a.collective_check["max_abs_diff"] <= 1e-4):
+            raise SystemExit(f"igs_allreduce_nvls disagrees with ncclAllReduce: {a.collective_check}")
 
     def step():
         if not backward:
@@ -401,7 +509,28 @@ def main():
                        "GaussianRasterizer(...) -> loss = <all heads, fixed weights> -> backward -> loss D2H"}
     else:
         e2e = {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    # the same step recorded once into CUDA graphs through the module API and replayed (one process per GPU,
+    # no collective inside the graph: N=1 only)
+    a.e2e_graph = None
+    if backward and not a.value_only and a.impl == "igs" and eff_world == 1 and not a.no_graph:
+        try:
+            from instag_b200 import rasterizer as R_
+            arm.build_graphs()
+            ms_g, _, _ = timed(torch, dist, arm.step_e2e_graph, a.steps, max(a.warmup, 3), flush, 1)
+            over = bool(R_.binding().captured_overflowed())
+            a.e2e_graph = {"value": 1000.0 / ms_g, "unit": "frames/s", "ms_per_step": ms_g,
+                           "h2d_bytes_per_step": arm.h2d_bytes, "d2h_bytes_per_step": 4,
+                           "instance_workspaces_overflowed": over, "loss": float(arm.loss_host[0]),
+                           "path": "the step of e2e (H2D of the next inputs on a forked stream, GaussianRasterizer(...), "
+                                   "loss, backward, loss D2H) recorded ONCE into two CUDA graphs through the module API "
+                                   "and replayed; instance counts held against the recorded workspaces after the run"}
+            if over:
+                a.e2e_graph["value"] = None
+        except Exception as ex:  # noqa: BLE001  (reported, not fatal: the eager e2e stands)
+            a.e2e_graph = {"value": None, "error": str(ex)[:300]}
 
+    if block is not None:
+        block.__exit__(None, None, None)  # the legs below allocate their own gradient blocks
     line = finish(a, cfg, sc, grads, arm, eff_world, rank, ms, per, wall, value, e2e, clocks, stages, frames, N,
                   launches_per_step if a.impl == "igs" else 0, backward, torch, dist, flush)
     if rank == 0:
@@ -409,6 +538,103 @@ def main():
     if world > 1 and a.impl == "igs":
         dist.barrier()
         dist.destroy_process_group()
+
+
+def face_pair(a, torch, dist, device, local):
+    """The real train_face.py step shape (gaussian_renderer/__init__.py:241-268, SURVEY 8d "also report
+    that pair"): ONE SH render of the face cloud (100k Gaussians, SH degree 1, M=4) with gradients into
+    every input, PLUS one `colors_precomp` attention render of the same cloud with detached geometry
+    (means3D / opacity / scales / rotations .detach()), both sharing one means2D tensor; loss over the
+    heads of the first render and the colour of the second; one backward.  Through the module API,
+    either arm; value = inputs resident in HBM, e2e = inputs from pinned host memory + loss D2H."""
+    import util as U
+    from instag_b200 import synthetic as S
+    cfg = dict(S.CONFIGS["C3_face"])
+    cloud = S.make_cloud(cfg["P"], sh_degree=1, M=4, seed=0)
+    sc = dict(cloud)
+    sc.update(S.make_camera(cfg["W"], cfg["H"]))
+    sc["bg"] = np.asarray(cfg["bg"], np.float32)
+    rng = np.random.default_rng(7)
+    sc["colors_precomp"] = None
+    attn = np.concatenate([rng.uniform(0, 1, (cfg["P"], 2)), np.zeros((cfg["P"], 1))], axis=1).astype(np.float32)
+    grads = S.upstream_grads(cfg["H"], cfg["W"], extra_dims=1, seed=1)
+    arm = Arm(a.impl, sc, grads, device)
+    attn_host = torch.from_numpy(attn).pin_memory()
+    attn_dev = [torch.empty_like(attn_host, device=device).requires_grad_(True) for _ in range(2)]
+    w_attn = torch.from_numpy(grads["color"]).to(device).reshape(-1)
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=device)
+
+    def body(leaves, attn_leaf):
+        m2 = torch.zeros_like(leaves["means3D"], requires_grad=True) + 0  # gaussian_renderer/__init__.py:159
+        m2.retain_grad()
+        rast = arm.Module(arm.rs)
+        color, depth, norm, alpha, radii, extra = rast(
+            means3D=leaves["means3D"], means2D=m2, shs=leaves["shs"], colors_precomp=None, opacities=leaves["opacities"],
+            scales=leaves["scales"], rotations=leaves["rotations"], cov3Ds_precomp=None,
+            extra_attrs=torch.ones_like(leaves["opacities"]))
+        attn_img = rast(means3D=leaves["means3D"].detach(), means2D=m2, shs=None, colors_precomp=attn_leaf,
+                        opacities=leaves["opacities"].detach(), scales=leaves["scales"].detach(),
+                        rotations=leaves["rotations"].detach(), cov3Ds_precomp=None,
+                        extra_attrs=torch.ones_like(leaves["opacities"]))[0]
+        loss = torch.dot(torch.cat([o.reshape(-1) for o in (color, depth, norm, alpha, extra)]), arm.wflat) + \
+            torch.dot(attn_img.reshape(-1), w_attn)
+        loss.backward()
+        return loss, m2
+
+    def step():
+        leaves = arm.leaves[0]
+        for v in leaves.values():
+            v.grad = None
+        attn_dev[0].grad = None
+        return body(leaves, attn_dev[0])
+
+    def step_e2e():
+        k = arm.cur
+        main = torch.cuda.current_stream(device)
+        main.wait_event(arm.ready[k])
+        arm._issue_copy(k ^ 1)
+        with torch.cuda.stream(arm.copy_stream):
+            attn_dev[k ^ 1].data.copy_(attn_host, non_blocking=True)
+            arm.ready[k ^ 1].record(arm.copy_stream)
+        leaves = arm.leaves[k]
+        for v in leaves.values():
+            v.grad = None
+        attn_dev[k].grad = None
+        loss, _ = body(leaves, attn_dev[k])
+        arm.free[k].record(main)
+        arm.loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+        arm.cur = k ^ 1
+
+    for t_ in attn_dev:
+        t_.data.copy_(attn_host)
+    sampler = ClockSampler(local)
+    step()
+    torch.cuda.synchronize()
+    sampler.start()
+    ms, per, wall = timed(torch, dist, step, a.steps, a.warmup, flush, 1)
+    ms_e2e, _, _ = timed(torch, dist, step_e2e, a.steps, max(a.warmup, 3), flush, 1)
+    clocks = sampler.result()
+    launches = 0
+    if a.impl == "igs":
+        from instag_b200 import _native as NV
+        l0 = NV.launch_count()
+        step()
+        torch.cuda.synchronize()
+        launches = NV.launch_count() - l0
+    print(json.dumps({
+        "metric": "train_face step shape: SH render + attention render sharing means2D, fwd+bwd, frames/sec @512^2",
+        "value": 1000.0 / ms, "unit": "frames/s", "n_gpus": 1, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "impl": a.impl,
+        "config": {"workload": "pair: face P=100000 Gaussians, 512x512; render 1 = SH deg 1 M=4, ED=1, all gradients; "
+                               "render 2 = colors_precomp attention map on detached geometry, same means2D; one backward "
+                               "(gaussian_renderer/__init__.py:241-268); through the module API, inputs resident in HBM",
+                   "l2": "flushed between steps (256 MiB memset outside the per-step event pairs)"},
+        "e2e": {"value": 1000.0 / ms_e2e, "unit": "frames/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": arm.h2d_bytes + attn.nbytes, "d2h_bytes_per_step": 4},
+        "clocks": clocks, "wall_s_timed_region": wall,
+        "ms_per_step_p10_p50_p90": [float(np.percentile(per, q)) for q in (10, 50, 90)],
+        "gpu_launches": launches * a.steps, "gpu_launches_per_step": launches}))
 
 
 def c3_pair(a, torch, dist, device, local):
@@ -491,39 +717,35 @@ def finish(a, cfg, sc, grads, arm, world, rank, ms, per, wall, value, e2e, clock
                    "timing": "sum of per-step CUDA-event pairs / K, max over ranks; the per-kernel (stages / roofline) "
                              "durations come from a second pass of the same K steps with CUDA events at the "
                              "stage boundaries"},
-        "e2e": e2e, "clocks": clocks, "wall_s_timed_region": wall,
+        "e2e": e2e, "e2e_graph": getattr(a, "e2e_graph", None), "clocks": clocks, "wall_s_timed_region": wall,
         "ms_per_step_p10_p50_p90": [float(np.percentile(per, q)) for q in (10, 50, 90)],
         "gpu_launches": int(launches) * a.steps,
         "gpu_launches_per_step": int(launches),
     }
     if a.impl == "reference":
         line["cpu_baseline"] = {"value": value, "unit": "frames/s", "cores": 0, "kind": "reference",
-                                "sample": "the UNMODIFIED reference CUDA rasterizer (oracle/_ref/libdgr_ref.so, "
-                                          "compiled for sm_100a) on the same GPU, whole frames; the reference has "
+                                "sample": "the UNMODIFIED reference CUDA rasterizer on the same GPU, whole frames, "
+                                          "through " + getattr(arm, "reference_host", "?") + "; the reference has "
                                           "no CPU implementation of this path"}
+        line["config"]["reference_host"] = getattr(arm, "reference_host", None)
         return line
-    # ---- roofline of the dominant kernel + per-stage table ----
-    alg = algorithmic_bytes(P, N, H * W, T, S=S_, c=1 if S_ else 0)
+    # ---- per-stage table: every kernel against ITS roof ----
+    c_ = 1 if S_ else 0
+    wl = "C5" if a.workload == "C5" else "C2"
+    alg = algorithmic_bytes(P, N, H * W, T, S=S_, c=c_)
     table = {}
     for k, t in stages.items():
         if t is None or t <= 0 or k not in alg:
             continue
         gbs = alg[k] / (t * 1e-3) / 1e9
-        table[k] = {"ms": t, "alg_bytes": int(alg[k]), "gbs": gbs, "frac_hbm": gbs / hbm_peak}
-    if table:
-        dom = max(table, key=lambda k: table[k]["ms"])
-        d = table[dom]
-        line["roofline"] = {"kernel": dom, "bound": "hbm", "achieved": d["gbs"], "peak": hbm_peak, "unit": "GB/s",
-                            "frac": d["frac_hbm"], "traffic": ncu_traffic(dom) if a.workload == "C2" else None,
-                            "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of the newest committed "
-                                              "profiles/r*_full.md (ncu --set full of this command), bytes per launch",
-                            "peak_source": peak_src,
-                            "alg_bytes_per_launch": d["alg_bytes"], "ms_per_launch": d["ms"],
-                            "frames_averaged": frames,
-                            "share_of_step": d["ms"] / sum(v["ms"] for v in table.values()),
-                            "note": "render / render_backward are FP32-issue bound, not HBM bound: see fp32"}
-        line["stages"] = table
-        line["stage_ms_sum"] = sum(v["ms"] for v in table.values())
+        table[k] = {"ms": t, "bound": BOUND_OF[k], "alg_bytes": int(alg[k]), "gbs": gbs, "frac_hbm": gbs / hbm_peak}
+        if a.workload in ("C2", "C5"):
+            table[k]["ncu_dram_bytes"] = ncu_traffic(k, wl)
+    line["stages"] = table
+    line["stage_ms_sum"] = sum(v["ms"] for v in table.values())
+    line["stage_timing"] = ("device-side stamps (%globaltimer of each kernel's last CTA; a stage runs from its "
+                            "predecessor's completion to its own): nothing sits between the kernels, the stages of "
+                            "a half add up to the half")
     # ---- CPU baseline (rank 0, N=1 only) + pair counts for the FP32 model ----
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
         cb, f = cpu_baseline(sc, grads, a.cpu_seconds, backward)
@@ -535,28 +757,61 @@ def finish(a, cfg, sc, grads, arm, world, rank, ms, per, wall, value, e2e, clock
         fp = {"pairs_evaluated": q_eval, "pairs_blended": q_acc, "pairs_evaluated_backward": q_eval_b,
               "peak_tflops_at_observed_clock": fp32_peak,
               "model": "fwd 15*Q_eval + 17*Q_acc, bwd 15*Q_eval' + 110*Q_acc flop (SURVEY 8d)"}
-        if "render" in table:
-            fl = 15 * q_eval + 17 * q_acc
-            fp["render_tflops"] = fl / (table["render"]["ms"] * 1e-3) / 1e12
-            fp["render_frac"] = fp["render_tflops"] / fp32_peak
-        if "render_backward" in table:
-            fl = 15 * q_eval_b + 110 * q_acc
-            fp["render_backward_tflops"] = fl / (table["render_backward"]["ms"] * 1e-3) / 1e12
-            fp["render_backward_frac"] = fp["render_backward_tflops"] / fp32_peak
+        for k, fl in (("render", 15 * q_eval + 17 * q_acc), ("render_backward", 15 * q_eval_b + 110 * q_acc)):
+            if k in table:
+                fp[k + "_tflops"] = fl / (table[k]["ms"] * 1e-3) / 1e12
+                fp[k + "_frac"] = fp[k + "_tflops"] / fp32_peak
+                table[k]["model_flop"] = int(fl)
+                table[k]["tflops"] = fp[k + "_tflops"]
+                table[k]["frac_fp32_peak"] = fp[k + "_frac"]
+                table[k]["issue_slots"] = ncu_issue(k, wl) if a.workload in ("C2", "C5") else None
         line["fp32"] = fp
+    # ---- roofline of the dominant kernel, on the roof that bounds it ----
+    if table:
+        dom = max(table, key=lambda k: table[k]["ms"])
+        d = table[dom]
+        share = d["ms"] / sum(v["ms"] for v in table.values())
+        common = {"kernel": dom, "bound": d["bound"], "ms_per_launch": d["ms"], "frames_averaged": frames,
+                  "share_of_step": share, "traffic": d.get("ncu_dram_bytes"),
+                  "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of the newest committed "
+                                    "profiles/r*_full.md (ncu --set full of this command), bytes per launch",
+                  "alg_bytes_per_launch": d["alg_bytes"], "hbm_gbs": d["gbs"], "hbm_frac": d["frac_hbm"]}
+        if d["bound"] == "fp32_issue" and "tflops" in d:
+            line["roofline"] = dict(common, achieved=d["tflops"], peak=line["fp32"]["peak_tflops_at_observed_clock"],
+                                    unit="TFLOP/s", frac=d["frac_fp32_peak"], issue_slots=d.get("issue_slots"),
+                                    model_flop_per_launch=d["model_flop"],
+                                    peak_source="148 SMs x 128 FP32 lanes x 2 flop x the SM clock observed during the run",
+                                    note="algorithmic flop (SURVEY 8d pair-count model, counted by the instrumented "
+                                         "oracle on this frame) / the kernel's measured duration; issue_slots is the "
+                                         "ncu view of the same kernel (share of all issue slots that issued)")
+        else:
+            line["roofline"] = dict(common, achieved=d["gbs"], peak=hbm_peak, unit="GB/s", frac=d["frac_hbm"],
+                                    peak_source=peak_src)
+    if getattr(a, "collective_check", None) is not None:
+        line["collective_check"] = a.collective_check
     # ---- auxiliary: forward-only synthesis fps (face 100k + mouth 30k per frame, frames sharded, no collective) ----
     if not a.no_synth and a.workload == "C2":
         line["synth"] = synth_fps(torch, dist, world, rank, flush, arm.device)
+    # ---- BASELINE config 5: 8 views of 1M Gaussians dealt to the ranks + ONE exchange of the packed gradients ----
+    if not a.no_c5 and a.workload == "C2" and not a.value_only:
+        line["c5"] = c5_leg(torch, dist, world, rank, arm.device, flush, getattr(a, "collective", "none"))
+    # ---- the kernels either side of the path ----
+    if not a.no_adjacent and a.workload == "C2" and world == 1 and not a.value_only:
+        line["adjacent"] = adjacent_kernels(torch, arm.device, flush)
     return line
 
 
 def cloud_from_ply(path):
     """A trained head in the reference's save_ply format (instag_b200/assets.py) as a bench cloud:
     raw parameters activated as gaussian_renderer/__init__.py:227-235 does (host side, once)."""
+    import torch
     from instag_b200 import assets as AS
-    from oracle import adjacent as A  # numpy activations; set-up only, outside every timed region
+    from instag_b200 import training_ops as TO
     g = AS.read_gaussian_ply(path)
-    means3D, scales, rotations, opac = A.activate(g["xyz"], None, g["scaling"], None, g["rotation"], None, g["opacity"])
+    dev = torch.device("cuda", torch.cuda.current_device())
+    tt = lambda x: torch.from_numpy(np.ascontiguousarray(x, np.float32)).to(dev)
+    means3D, scales, rotations, opac = (t.cpu().numpy() for t in TO.activate_gaussians(
+        tt(g["xyz"]), tt(g["scaling"]), tt(g["rotation"]), tt(g["opacity"]).reshape(-1, 1)))
     shs = np.ascontiguousarray(np.concatenate([g["features_dc"], g["features_rest"]], axis=1), np.float32)
     return dict(means3D=means3D, scales=scales, rotations=rotations, opacities=opac.reshape(-1, 1),
                 extra_attrs=np.ones((means3D.shape[0], 1), np.float32), shs=shs, colors_precomp=None,
@@ -635,6 +890,168 @@ def synth_fps(torch, dist, world, rank, flush, device, total_frames=1000):
             "workload": "face 100k + mouth 30k Gaussians (SH deg 1, M=4), 512x512, forward only (the two passes "
                         "of a frame on two streams, instance counts read when the frame is harvested) + fused compose (igs_compose_frame) into a device ring, uint8 frames copied to pinned memory on a side "
                         "stream; " + f"{frames * world} frames sharded over {world} rank(s), no collective"}
+
+
+
+def c5_leg(torch, dist, world, rank, device, flush, collective, steps=6, warmup=2):
+    """BASELINE config 5: ONE training batch of 8 views of a 1M-Gaussian cloud at
+    1024^2, SH degree 3 (M=16), forward + backward, the views dealt to the ranks (rank r: views r,
+    r+world, ...), the per-Gaussian parameter gradients of a rank's views added up locally and then
+    summed over the ranks by ONE collective over the packed block (252 MB: igs_allreduce_nvls over
+    NVLink multicast memory, or NCCL).  value = 8 views / step time; world = 1 renders the 8 views in
+    turn with no exchange -- the line the driver's efficiency column is relative to."""
+    import util as U
+    from instag_b200 import synthetic as S
+    from instag_b200 import rasterizer as R
+    from instag_b200 import sharding as SHD
+    cfg = S.CONFIGS["C5"]
+    P, H, W, M = cfg["P"], cfg["H"], cfg["W"], cfg["M"]
+    cloud = S.make_cloud(P, sh_degree=cfg["sh_degree"], M=M, seed=0)
+    views = 8
+    mine = SHD.shard_indices(views, rank, world)
+    cams = S.camera_sequence(views, W, H, seed=5)
+    tcl = U.to_torch(cloud, device)
+    bg = torch.tensor(cfg["bg"], dtype=torch.float32, device=device)
+    scenes = []
+    for v in mine:
+        t = dict(tcl)
+        t.update(U.to_torch(cams[v], device))
+        t["bg"] = bg
+        scenes.append((U.raw_args_fwd(t), t))
+    tg = {k: torch.from_numpy(v).to(device) for k, v in S.upstream_grads(H, W, extra_dims=1, seed=1).items()}
+    _, _, total, param_end = R.gradient_layout(P, M, 1)
+    block = None
+    if world > 1 and "igs_allreduce_nvls" in collective:
+        block = SHD.NvlsGradientBlock(P, M, 1, device)
+    ev = [[torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)] for _ in range(steps + warmup)]
+    it = iter(range(10 ** 9))
+    counts = []
+
+    def step():
+        k = next(it) % len(ev)
+        acc = None
+        for i, (fargs, t) in enumerate(scenes):
+            n, color, depth, norm, alpha, radii, extra, geom, binb, img = R._forward_native(*fargs)
+            first = i == 0
+            if first and block is not None:
+                block.__enter__()  # the first view's gradients are written straight into the multicast buffer
+            try:
+                res = R._backward_native(*U._bwd_args(t, radii, tg, geom, n, binb, img, alpha))
+            finally:
+                if first and block is not None:
+                    block.__exit__(None, None, None)
+            flat = SHD.packed_base(res[1])
+            if first:
+                acc = flat
+                counts[:] = [int(n)]
+            else:
+                acc[:param_end].add_(flat[:param_end])  # a rank's views add up locally before the exchange
+        ev[k][0].record()
+        if world > 1:
+            if block is not None:
+                block.all_reduce()
+            else:
+                dist.all_reduce(acc[:param_end])
+        ev[k][1].record()
+        return acc
+
+    ms, per, _ = timed(torch, dist, step, steps, warmup, flush, world)
+    torch.cuda.synchronize()
+    ex = float(np.mean([a_.elapsed_time(b_) for a_, b_ in ev[warmup:warmup + steps]]))
+    if world > 1:
+        t_ = torch.tensor([ex], device=device, dtype=torch.float64)
+        dist.all_reduce(t_, op=dist.ReduceOp.MAX)
+        ex = float(t_.item())
+    out = {"value": views * 1000.0 / ms, "unit": "frames/s", "ms_per_step": ms, "views_per_step": views,
+           "views_per_rank": len(mine), "exchange_ms": ex if world > 1 else 0.0,
+           "exchanged_bytes_per_rank": int(param_end * 4) if world > 1 else 0,
+           "collective": collective if world > 1 else "none", "num_rendered_first_view": counts[0] if counts else None,
+           "workload": f"C5: {views} views of P={P} Gaussians, {W}x{H}, SH deg {cfg['sh_degree']} M={M}, ED=1, "
+                       f"forward+backward, views dealt to {world} rank(s); exchange_ms is measured by CUDA events "
+                       f"around the collective inside the step (max over ranks) and is fully exposed: every gradient "
+                       f"of a view is produced by the last kernel of its backward"}
+    if world > 1:
+        out["exchange_gbs_algorithmic"] = param_end * 4 / (ex * 1e-3) / 1e9 if ex > 0 else None
+    return out
+
+
+def collective_check(torch, dist, block, device):
+    """Once, outside every timed region: igs_allreduce_nvls against ncclAllReduce on the same data."""
+    g = torch.Generator(device=device).manual_seed(1234 + dist.get_rank())
+    worst, identical = 0.0, True
+    for _ in range(3):
+        src = torch.randn(block.total, device=device, generator=g)
+        want = src.clone()
+        dist.all_reduce(want[:block.param_end])
+        buf = block._alloc(block.total, device)
+        buf.copy_(src)
+        torch.cuda.synchronize()
+        dist.barrier()
+        out = block.all_reduce()
+        torch.cuda.synchronize()
+        dist.barrier()
+        diff = (out[:block.param_end] - want[:block.param_end]).abs().max()
+        same = torch.equal(out[:block.param_end], want[:block.param_end]) and torch.equal(out[block.param_end:], src[block.param_end:])
+        t = torch.tensor([float(diff), 0.0 if same else 1.0], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        worst, identical = max(worst, float(t[0])), identical and float(t[1]) == 0.0
+    return {"max_abs_diff": worst, "bit_identical": identical, "floats": int(block.param_end), "rounds": 3,
+            "against": "dist.all_reduce (NCCL) of a copy of the same buffer"}
+
+
+def adjacent_kernels(torch, device, flush, reps=20):
+    """Throughput of the kernels either side of the path (f1 compose, f2 activations and
+    densification statistics, f3 L1 + D-SSIM), each against the HBM roof it is bound by: algorithmic
+    bytes / CUDA-event time, L2 flushed before every launch; at the size the path runs them (512^2
+    frame, 100k Gaussians: launch-latency bound) and at a size that fills the machine."""
+    from instag_b200 import synthesis as SY
+    from instag_b200 import training_ops as TO
+    from instag_b200 import losses as LS
+    hbm_peak, _, _ = load_peaks()
+    out = {}
+
+    def run(name, fn, nbytes):
+        for _ in range(3):
+            fn()
+        ts = []
+        for _ in range(reps):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        ms = float(np.median(ts))
+        out[name] = {"ms": ms, "alg_bytes": int(nbytes), "gbs": nbytes / (ms * 1e-3) / 1e9,
+                     "frac_hbm": nbytes / (ms * 1e-3) / 1e9 / hbm_peak, "bound": "hbm"}
+
+    g = torch.Generator(device=device).manual_seed(0)
+    rnd = lambda *sh: torch.rand(*sh, device=device, generator=g)
+    for tag, side, P in (("", 512, 100_000), ("_large", 2048, 4_000_000)):
+        fr, fa, mr, ma, bgi = rnd(3, side, side), rnd(1, side, side), rnd(3, side, side), rnd(1, side, side), rnd(3, side, side) * 255
+        slot = torch.empty((side, side, 3), dtype=torch.uint8, device=device)
+        run("compose_frame" + tag, lambda: SY.compose_frame(fr, fa, mr, ma, bgi, out=slot), side * side * (11 * 4 + 3))
+        run("compose_frame_dilate" + tag, lambda: SY.compose_frame(fr, fa, mr, ma, bgi, dilate=True, out=slot),
+            side * side * (11 * 4 + 3))
+        xyz, scal, rot, opa = rnd(P, 3), rnd(P, 3), rnd(P, 4), rnd(P, 1)
+        dx, ds, dr = rnd(P, 3), rnd(P, 3), rnd(P, 4)
+        with torch.no_grad():
+            run("activate_forward" + tag, lambda: TO.activate_gaussians(xyz, scal, rot, opa, dx, ds, dr), P * 4 * (21 + 11))
+        leaves = [t.clone().requires_grad_(True) for t in (xyz, scal, rot, opa)]
+        outs = TO.activate_gaussians(*leaves, dx, ds, dr)
+        gs = [torch.ones_like(o) for o in outs]
+        run("activate_backward" + tag, lambda: torch.autograd.grad(outs, leaves, gs, retain_graph=True), P * 4 * (18 + 11 + 11))
+        radii = (torch.rand(P, device=device, generator=g) * 20).to(torch.int32)
+        gm, mr2, acc, den = rnd(P, 3), torch.zeros(P, device=device), torch.zeros(P, 1, device=device), torch.zeros(P, 1, device=device)
+        run("densify_stats" + tag, lambda: TO.add_densification_stats(radii, gm, mr2, acc, den), P * (4 + 12 + 3 * 8))
+        img = rnd(3, side, side).requires_grad_(True)
+        gt = rnd(3, side, side)
+        with torch.no_grad():
+            run("l1_ssim_forward" + tag, lambda: LS.l1_ssim_loss(img, gt), 3 * side * side * 4 * (2 + 3))
+        loss = LS.l1_ssim_loss(img, gt)
+        run("l1_ssim_backward" + tag, lambda: torch.autograd.grad(loss, img, retain_graph=True), 3 * side * side * 4 * (5 + 1))
+    out["note"] = ("host wrappers included (one autograd.Function call per launch; l1_ssim_forward also sums its "
+                   "per-CTA partials with torch); *_large = 2048^2 frame / 4M Gaussians")
+    return out
 
 
 def reference_cpu_arm(a, sc, grads, backward, cfg):

@@ -97,6 +97,66 @@ def make_cloud(P, sh_degree=None, M=None, seed=0, extra_dims=1, scale_mult=1.0, 
     return cloud
 
 
+def make_shell_cloud(P, sh_degree=None, M=None, seed=0, extra_dims=1, radii=(0.075, 0.1, 0.09), thickness=0.002,
+                     opaque=True):
+    """A trained head is not a filled cube but a thin surface shell: points on an ellipsoid of
+    half-axes `radii` (a head-sized 15 x 20 x 18 cm) displaced along the normal by N(0, thickness),
+    flat splats (one scale axis 5x smaller than the other two), and, with `opaque`, the bimodal
+    opacity of a converged model (most splats near 1, a tail near 0).  Front and back surface overlap
+    on screen, the silhouette is seen at grazing angles: longer lists per tile than the uniform cube,
+    and pixels that saturate after a few dozen entries.  Same dictionary as make_cloud."""
+    rng = np.random.default_rng(seed)
+    f = np.float32
+    d = rng.normal(0.0, 1.0, (P, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True) + 1e-12
+    means = (d * np.asarray(radii) * (1.0 + rng.normal(0.0, thickness / min(radii), (P, 1)))).astype(f)
+    area = 4.0 * math.pi * ((radii[0] * radii[1]) ** 1.6 / 3 + (radii[0] * radii[2]) ** 1.6 / 3 +
+                            (radii[1] * radii[2]) ** 1.6 / 3) ** (1 / 1.6)
+    s0 = 1.1 * math.sqrt(area / max(P, 1))            # splats about as large as their spacing on the surface
+    scales = s0 * np.exp(rng.normal(0.0, 0.4, (P, 3)))
+    scales[np.arange(P), rng.integers(0, 3, P)] *= 0.2
+    q = rng.normal(0.0, 1.0, (P, 4))
+    q /= np.linalg.norm(q, axis=1, keepdims=True) + 1e-12
+    logit = np.where(rng.uniform(size=(P, 1)) < 0.8, rng.normal(4.0, 1.5, (P, 1)), rng.normal(-3.0, 1.5, (P, 1))) \
+        if opaque else rng.normal(0.0, 2.0, (P, 1))
+    opac = (1.0 / (1.0 + np.exp(-logit))).astype(f)
+    cloud = dict(means3D=means, scales=scales.astype(f), rotations=q.astype(f), opacities=opac,
+                 extra_attrs=np.ones((P, extra_dims), f) if extra_dims else None,
+                 shs=None, colors_precomp=None, sh_degree=0)
+    if sh_degree is None:
+        cloud["colors_precomp"] = rng.uniform(0.0, 1.0, (P, 3)).astype(f)
+    else:
+        M = (sh_degree + 1) ** 2 if M is None else M
+        shs = rng.normal(0.0, 0.1, (P, M, 3))
+        shs[:, 0, :] = rng.normal(0.0, 0.5, (P, 3))
+        cloud["shs"] = shs.astype(f)
+        cloud["sh_degree"] = sh_degree
+    return cloud
+
+
+def make_opacity_extreme_cloud(P, seed=0, **kw):
+    """The uniform cloud with opacities pushed to the two ends the kernels special-case: a third
+    exactly 1.0 (alpha clamps at 0.99 on every pixel near the centre), a third around 1/255 (the
+    blend threshold decides pixel by pixel), a third ordinary."""
+    cloud = make_cloud(P, seed=seed, **kw)
+    rng = np.random.default_rng(seed + 77)
+    which = rng.integers(0, 3, (P, 1))
+    op = cloud["opacities"]
+    op = np.where(which == 0, 1.0, np.where(which == 1, rng.uniform(0.5 / 255, 3.0 / 255, (P, 1)), op))
+    cloud["opacities"] = op.astype(np.float32)
+    return cloud
+
+
+def make_concentrated_cloud(P, seed=0, extent=0.02, **kw):
+    """Every instance in a few dozen tiles: the cloud of make_cloud squeezed into a cube of half-width
+    `extent` (64 px across at 512^2: 4 x 4 tiles and their border, 64 tiles at most) with the splat sizes of the
+    head-sized cloud, so that lists run to many thousands of entries per tile -- the per-tile sort's
+    two-level path and the render kernels' long units."""
+    cloud = make_cloud(P, seed=seed, **kw)
+    cloud["means3D"] = (cloud["means3D"] * (extent / kw.get("extent", 0.1))).astype(np.float32)
+    return cloud
+
+
 def upstream_grads(H, W, extra_dims=1, seed=1):
     """Fixed random dL/d(output) images so that every head receives gradient
     (loss = sum w*out, as the mix of losses in train_face.py:456-540 does)."""
@@ -114,7 +174,26 @@ CONFIGS = {
     "C3_mouth": dict(P=30_000, W=512, H=512, sh_degree=1, M=4, backward=True, bg=(0.0, 1.0, 0.0)),
     "C3_face": dict(P=100_000, W=512, H=512, sh_degree=1, M=4, backward=True, bg=(0.0, 1.0, 0.0)),
     "C5": dict(P=1_000_000, W=1024, H=1024, sh_degree=3, M=16, backward=True, bg=(0.0, 1.0, 0.0)),
+    # not BASELINE configs: other input distributions at the C2 shape (VERDICT r01 "one input distribution")
+    "shell": dict(P=100_000, W=512, H=512, sh_degree=None, M=0, backward=True, bg=(0.0, 1.0, 0.0), cloud="shell"),
+    "concentrated": dict(P=100_000, W=512, H=512, sh_degree=None, M=0, backward=True, bg=(0.0, 1.0, 0.0),
+                         cloud="concentrated"),
+    "opacity_extreme": dict(P=100_000, W=512, H=512, sh_degree=None, M=0, backward=True, bg=(0.0, 1.0, 0.0),
+                            cloud="opacity_extreme"),
 }
+
+
+def cloud_for(cfg, seed=0):
+    """The cloud a CONFIGS entry names (default: the SURVEY 8d uniform cube)."""
+    kind = cfg.get("cloud", "uniform")
+    kw = dict(sh_degree=cfg["sh_degree"], M=cfg["M"] or None)
+    if kind == "shell":
+        return make_shell_cloud(cfg["P"], seed=seed, **kw)
+    if kind == "concentrated":
+        return make_concentrated_cloud(cfg["P"], seed=seed, **kw)
+    if kind == "opacity_extreme":
+        return make_opacity_extreme_cloud(cfg["P"], seed=seed, **kw)
+    return make_cloud(cfg["P"], seed=seed, **kw)
 
 
 def make_config(name, seed=0, P=None):

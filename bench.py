@@ -101,6 +101,7 @@ class ClockSampler(threading.Thread):
 
 
 KERNEL_OF = {"preprocess": "preprocess_kernel", "duplicate": "duplicate_kernel", "sort": "tile_sort_kernel",
+
              "render": "render_kernel", "render_backward": "render_backward_kernel",
              "preprocess_backward": "preprocess_backward_kernel"}
 # which roof bounds which kernel: HBM for the per-Gaussian / binning kernels, FP32 instruction
@@ -158,14 +159,15 @@ def ncu_issue(stage, workload="C2"):
 def algorithmic_bytes(P, N, HW, T, S=0, c=0, ED=1):
     """Per-stage algorithmic bytes with this library's record sizes (DESIGN.md "Kernels"): what each
     kernel has to move once.  preprocess reads 44(+12S) B per Gaussian and writes the 64 B splat record
-    + radii + tiles_touched (+1 clamp); duplicate reads 24 B per Gaussian and the T tile counts, writes
-    one 8 B word per instance, the tile ranges and the tile order; the tile sort reads the words and
+    + radii + tiles_touched (+1 clamp), and its last CTA turns the T tile counts into ranges and
+    cursors; duplicate reads 24 B per Gaussian and writes one 8 B word per instance (+ the tile order);
+    the tile sort reads the words and
     writes point_list; render reads 4+64 B per instance and writes the images; render backward
     reads the same + the upstream images and adds into the 64 B accumulator rows; the per-Gaussian
     backward reads accumulator + record + inputs and writes every gradient."""
     return {
-        "preprocess": (44 + 12 * S + 64 + 8 + c) * P,
-        "duplicate": 24 * P + 8 * N + 16 * T,
+        "preprocess": (44 + 12 * S + 64 + 8 + c) * P + 16 * T,
+        "duplicate": 24 * P + 8 * N + 8 * T,
         "sort": 8 * N + 4 * N,
         "render": (4 + 64) * N + (4 * (8 + ED) + 4) * HW,
         "render_backward": (4 + 64) * N + (8 + 4 * (8 + ED)) * HW + 2 * 64 * P,

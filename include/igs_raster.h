@@ -221,7 +221,7 @@ int igs_backward(const IgsBwdArgs* args, igs_stream_t stream);
  * igs_profile_read synchronises the device and returns the MEAN stage durations in ms over the frames
  * recorded since igs_profile_enable(1) (-1 = stage did not run).  A stage lasts from the completion of
  * its predecessor to its own completion, so the stages of a half add up to the half: 0 preprocess (from
- * its first CTA's start), 1 duplicate + tile ranges, 2 per-tile depth sort, 3 (unused), 4 render,
+ * its first CTA's start; its last CTA also makes the tile ranges), 1 duplicate, 2 per-tile depth sort, 3 (unused), 4 render,
  * 5 render backward (from its first CTA's start), 6 per-Gaussian backward.  igs_launch_count returns how
  * many kernels this host thread has launched through the library so far. */
 #define IGS_NUM_STAGES 7

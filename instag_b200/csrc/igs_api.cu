@@ -167,12 +167,18 @@ static BinArgs make_bin(const IgsFwdArgs* a) {
   ba.splat = (const float4*)(g + gl.splat);
   ba.tiles_touched = (const uint32_t*)(g + gl.tiles_touched);
   ba.header = (CtrlHeader*)(c + cl.header);
-  ba.num_rendered_host = device_view_of_pinned(a->num_rendered_pinned);
   ba.tile_count = (uint32_t*)(c + cl.tile_count);
   ba.tile_cursor = (uint32_t*)(c + cl.tile_cursor);
-  ba.ranges = (uint2*)(im + il.ranges);
+  ba.ranges = (const uint2*)(im + il.ranges);
   ba.tile_order = (uint32_t*)(im + il.tile_order);
-  ba.info = (uint32_t*)(im + il.info);
+  ba.scan.num_tiles = ba.num_tiles;
+  ba.scan.capacity = a->capacity;
+  ba.scan.header = ba.header;
+  ba.scan.num_rendered_host = device_view_of_pinned(a->num_rendered_pinned);
+  ba.scan.info = (uint32_t*)(im + il.info);
+  ba.scan.tile_count = ba.tile_count;
+  ba.scan.tile_cursor = ba.tile_cursor;
+  ba.scan.ranges = (uint2*)(im + il.ranges);
   ba.pairs = (unsigned long long*)(so + sl.pairs);
   ba.pairs2 = (unsigned long long*)(so + sl.pairs2);
   ba.point_list = (uint32_t*)(b + bl.point_list);

@@ -9,13 +9,16 @@
 // is a drop-in.  Here the tile part of the sort is done by COUNTING:
 //   preprocess_kernel   counts the instances of every tile while it computes the tile
 //                       rectangles (igs_preprocess.cu);
-//   duplicate_kernel    every CTA scans the T tile counts itself (a few KB out of L2) and so
-//                       knows where each tile's segment starts -- no single-CTA scan sits
-//                       between the two kernels -- then drops each instance of its 512
-//                       Gaussians straight into its tile's segment as one 64-bit word
-//                       depth_bits<<32 | gaussian_id.  CTA 0 has no Gaussians: it writes the
-//                       tile ranges, the tile order of the render kernels and num_rendered
-//                       (identifyTileRanges + the reference's 4-byte readback);
+//   tile ranges         identifyTileRanges + the reference's 4-byte num_rendered readback
+//                       (igs_tile_scan.cuh): the exclusive scan of the T counts.  Up to 2048
+//                       tiles every duplicate CTA does that scan for itself and a service CTA
+//                       writes the ranges; above, a one-CTA tile_scan_kernel runs in front.
+//                       (Measured and dropped: the preprocess CTA that finishes last doing it --
+//                       the fence + counter every CTA needs cost 4 us at C2 and 22 us at C5.)
+//   duplicate_kernel    drops each instance of its 512 Gaussians straight into its tile's
+//                       segment (slot = the tile's cursor) as one 64-bit word
+//                       depth_bits<<32 | gaussian_id; its service CTA files the tiles by list
+//                       length for the render kernels;
 //   tile_sort_kernel    one CTA per tile sorts the segment by that word in shared memory
 //                       and writes point_list (+ the reference's 64-bit keys on request).
 // Sorting by (depth, id) reproduces the reference's stable order: inside one tile the
@@ -27,13 +30,11 @@
 // tile sort 8N read + 4N written (+ 8N with keys).
 #include "igs_common.cuh"
 #include "igs_kernels.cuh"
+#include "igs_tile_scan.cuh"
 
 namespace igs {
 
-constexpr int DUP_THREADS = PRE_THREADS;
-constexpr int DUP_WARPS = DUP_THREADS / 32;
 constexpr int ORDER_BUCKETS = 2 * DUP_THREADS;
-constexpr int DUP_REG_TILES = 8; // tile counts a thread keeps in registers between its two passes (T <= 4096)
 
 // One warp per 32 Gaussians; the warp's instances are spread evenly over the lanes
 // (a lane finds the Gaussian that owns instance k by a 5-step search over the warp's
@@ -74,36 +75,9 @@ __device__ __forceinline__ void for_each_instance(uint32_t n, uint32_t xy, uint3
   }
 }
 
-// exclusive prefix of one value per thread over the CTA (DUP_THREADS threads); *total = the sum.
-// Two barriers; s_warp is free for reuse after the call's second barrier has been passed by all.
-__device__ __forceinline__ uint32_t cta_exclusive_scan(uint32_t v, uint32_t* s_warp, uint32_t* total) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  uint32_t inc = v;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
-    if (lane >= o) inc += n;
-  }
-  __syncthreads(); // s_warp may still be read from an earlier call
-  if (lane == 31) s_warp[warp] = inc;
-  __syncthreads();
-  uint32_t run = inc - v, all = 0;
-#pragma unroll
-  for (int w = 0; w < DUP_WARPS; w++) {
-    const uint32_t s = s_warp[w];
-    if (w < warp) run += s;
-    all += s;
-  }
-  *total = all;
-  return run;
-}
-
-// Tile counts -> tile ranges (reference identifyTileRanges, rasterizer_impl.cu:116-138 + the
-// memset at :313: [exclusive prefix of the counts, +count), (0,0) for an empty tile),
-// num_rendered, the overflow flag, and the unit order of the render kernels (tiles with the
-// longest lists first: their warps are the critical path).  One CTA.  abs_cursors: also
-// seed tile_cursor with the segment starts (the global-memory duplicate path).
-__device__ void tile_service(const BinArgs& a, const bool abs_cursors) {
+// The unit order of the render kernels: tiles with the longest lists first (their warps are the
+// critical path), by one counting pass over ORDER_BUCKETS count classes.  One CTA.
+__device__ void tile_order(const BinArgs& a) {
   __shared__ uint32_t s_bucket[ORDER_BUCKETS];
   __shared__ uint32_t s_warp[DUP_WARPS], s_max[DUP_WARPS];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -111,34 +85,17 @@ __device__ void tile_service(const BinArgs& a, const bool abs_cursors) {
   const int per = (T + DUP_THREADS - 1) / DUP_THREADS;
   const int t0 = min(T, tid * per), t1 = min(T, t0 + per);
 #define TILE_CNT(t) __ldcg(a.tile_count + (size_t)(t) * CNT_STRIDE)
-  uint32_t sum = 0, cmax = 0;
-  for (int t = t0; t < t1; t++) { const uint32_t c = TILE_CNT(t); sum += c; cmax = max(cmax, c); }
+  uint32_t cmax = 0;
+  for (int t = t0; t < t1; t++) cmax = max(cmax, TILE_CNT(t));
   for (int b = tid; b < ORDER_BUCKETS; b += DUP_THREADS) s_bucket[b] = 0u;
   cmax = __reduce_max_sync(0xffffffffu, cmax);
   if (lane == 0) s_max[warp] = cmax;
-  uint32_t total;
-  uint32_t run = cta_exclusive_scan(sum, s_warp, &total);
-  if (tid == 0) {
-    a.header->num_rendered = total;
-    a.header->overflow = (int64_t)total > a.capacity ? 1u : 0u;
-    a.header->render_ticket = 0u;
-    a.info[0] = total;
-    // straight into the caller's pinned host slot: a 4-byte copy-engine transfer between two kernels
-    // costs ~12 us of stream time on B200, a posted store costs nothing (the host polls this slot, or
-    // reads it when it next needs the count)
-    if (a.num_rendered_host) *(volatile int32_t*)a.num_rendered_host = (int32_t)total;
-  }
+  __syncthreads();
 #pragma unroll
   for (int w = 0; w < DUP_WARPS; w++) cmax = max(cmax, s_max[w]);
   const float qs = (float)(ORDER_BUCKETS - 1) / (float)max(cmax, 1u);
 #define ORDER_BUCKET(c) ((ORDER_BUCKETS - 1) - min(ORDER_BUCKETS - 1, (int)((float)(c) * qs)))
-  for (int t = t0; t < t1; t++) {
-    const uint32_t c = TILE_CNT(t);
-    if (abs_cursors) a.tile_cursor[(size_t)t * CNT_STRIDE] = run;
-    a.ranges[t] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
-    run += c;
-    atomicAdd(&s_bucket[ORDER_BUCKET(c)], 1u);
-  }
+  for (int t = t0; t < t1; t++) atomicAdd(&s_bucket[ORDER_BUCKET(TILE_CNT(t))], 1u);
   { // exclusive scan of the bucket sizes (ORDER_BUCKETS == 2 * DUP_THREADS: two per thread)
     __syncthreads();
     const uint32_t c0 = s_bucket[2 * tid], c1 = s_bucket[2 * tid + 1];
@@ -156,50 +113,59 @@ __device__ void tile_service(const BinArgs& a, const bool abs_cursors) {
 #undef TILE_CNT
 }
 
+// Who turns the tile counts into segment starts.  Up to this many tiles every duplicate CTA scans
+// the counts itself (a few KB out of L2, in parallel: nothing single-CTA sits between the two kernels)
+// and CTA 0, which has no Gaussians, writes ranges / order / num_rendered for the kernels behind.
+// Above, that redundancy costs more than it saves (4096 tiles x 1954 CTAs re-read 256 MB: 103 us
+// against 67 + 11), and a one-CTA tile_scan_kernel in front seeds absolute cursors instead.
+constexpr int SCAN_IN_DUP_MAX_TILES = 2048;
+
 __global__ void __launch_bounds__(DUP_THREADS) tile_scan_kernel(BinArgs a) {
   if (a.prof.early) pdl_launch_dependents();
-  pdl_wait();
-  tile_service(a, true);
+  pdl_wait(); // the preprocess kernel's tile counts
+  tile_ranges(a.scan, true);
 }
 
 // HIST_SMEM: the CTA first counts its instances per tile in shared memory, reserves one
 // contiguous run of slots per non-empty tile with a single global atomic, and then hands
 // the slots out with shared-memory atomics -- N/(instances a CTA has per tile) global
 // atomics instead of N.  (The order inside a tile segment is irrelevant: tile_sort_kernel
-// sorts it by unique words.)  The segment starts come from the CTA's own scan of the tile
-// counts; CTA 0 is the service CTA (tile_service).
-template <bool HIST_SMEM>
+// sorts it by unique words.)  OWN_SCAN: see SCAN_IN_DUP_MAX_TILES; the tile cursors are then
+// relative to the segment starts the CTA has worked out for itself.  One CTA of the grid has no
+// Gaussians: it files the tiles by list length for the render kernels (and, with OWN_SCAN, writes the
+// tile ranges first).
+template <bool HIST_SMEM, bool OWN_SCAN>
 __global__ void __launch_bounds__(DUP_THREADS) duplicate_kernel(BinArgs a) {
   extern __shared__ uint32_t s_slot[];
   __shared__ uint32_t s_scan[DUP_WARPS];
   const int tid = threadIdx.x, lane = tid & 31;
   const int T = a.num_tiles;
+  const bool service = blockIdx.x == 0;
   if (a.prof.early) pdl_launch_dependents();
-  if (HIST_SMEM && blockIdx.x != 0)
+  if (HIST_SMEM && !service)
     for (int t = tid; t < T; t += DUP_THREADS) s_slot[t] = 0u;
-  pdl_wait(); // everything below reads what the preprocess kernel wrote
-  if (HIST_SMEM && blockIdx.x == 0) {
-    tile_service(a, false);
+  pdl_wait(); // everything below reads what the preprocess (and tile-scan) kernel wrote
+  if (service) {
+    if (OWN_SCAN) tile_ranges(a.scan, false);
+    tile_order(a);
     if (tid == 0) stamp_done(a.prof, ST_DUP);
     return;
   }
-  const int g = (int)(blockIdx.x - (HIST_SMEM ? 1 : 0)) * DUP_THREADS + tid;
+  if (!OWN_SCAN && __ldcg(&a.header->overflow)) return; // the frame does not fit: nothing is placed
+  const int g = (int)(blockIdx.x - 1) * DUP_THREADS + tid;
   uint32_t n = 0, xy = 0, w = 1, depth = 0;
   if (g < a.P) n = __ldg(a.tiles_touched + g);
-  // this thread's run of tiles in the CTA's scan of the tile counts (requested before the
+  // OWN_SCAN: this thread's run of tiles in the CTA's scan of the tile counts (requested before the
   // Gaussian's data is used, so that the two L2 round trips overlap)
   const int per = (T + DUP_THREADS - 1) / DUP_THREADS;
   const int t0 = min(T, tid * per), t1 = min(T, t0 + per);
   uint32_t cnt[DUP_REG_TILES], sum = 0;
-  if (HIST_SMEM) {
-    if (per <= DUP_REG_TILES) {
+  if (OWN_SCAN) {
+    static_assert(SCAN_IN_DUP_MAX_TILES <= DUP_REG_TILES * DUP_THREADS, "the counts of a thread's tiles stay in registers");
 #pragma unroll
-      for (int k = 0; k < DUP_REG_TILES; k++) {
-        cnt[k] = t0 + k < t1 ? __ldcg(a.tile_count + (size_t)(t0 + k) * CNT_STRIDE) : 0u;
-        sum += cnt[k];
-      }
-    } else {
-      for (int t = t0; t < t1; t++) sum += __ldcg(a.tile_count + (size_t)t * CNT_STRIDE);
+    for (int k = 0; k < DUP_REG_TILES; k++) {
+      cnt[k] = t0 + k < t1 ? __ldcg(a.tile_count + (size_t)(t0 + k) * CNT_STRIDE) : 0u;
+      sum += cnt[k];
     }
   }
   if (n) {
@@ -215,10 +181,10 @@ __global__ void __launch_bounds__(DUP_THREADS) duplicate_kernel(BinArgs a) {
     __syncthreads();
     for_each_instance(n, xy, w, depth, gbase, a.grid_x,
                       [&](uint32_t t, unsigned long long) { atomicAdd(&s_slot[t], 1u); });
-    uint32_t total;
-    uint32_t run = cta_exclusive_scan(sum, s_scan, &total); // (its barriers also order the shared-memory atomics)
-    if ((int64_t)total > a.capacity) return; // the frame does not fit: nothing is placed (uniform over the grid)
-    if (per <= DUP_REG_TILES) {
+    if (OWN_SCAN) {
+      uint32_t total;
+      uint32_t run = cta_exclusive_scan(sum, s_scan, &total); // (its barriers also order the shared-memory atomics)
+      if ((int64_t)total > a.capacity) return; // the frame does not fit: nothing is placed (uniform over the grid)
 #pragma unroll
       for (int k = 0; k < DUP_REG_TILES; k++) {
         if (t0 + k < t1) {
@@ -228,24 +194,22 @@ __global__ void __launch_bounds__(DUP_THREADS) duplicate_kernel(BinArgs a) {
         }
       }
     } else {
-      for (int t = t0; t < t1; t++) {
+      __syncthreads();
+      for (int t = tid; t < T; t += DUP_THREADS) {
         const uint32_t c = s_slot[t];
-        if (c) s_slot[t] = run + atomicAdd(a.tile_cursor + (size_t)t * CNT_STRIDE, c);
-        run += __ldcg(a.tile_count + (size_t)t * CNT_STRIDE);
+        if (c) s_slot[t] = atomicAdd(a.tile_cursor + (size_t)t * CNT_STRIDE, c);
       }
     }
     __syncthreads();
     for_each_instance(n, xy, w, depth, gbase, a.grid_x, [&](uint32_t t, unsigned long long word) {
       a.pairs[atomicAdd(&s_slot[t], 1u)] = word;
     });
-    if (tid == 0) stamp_done(a.prof, ST_DUP);
   } else {
-    if (__ldcg(&a.header->overflow)) return; // (written by tile_scan_kernel, which ran before this grid)
     for_each_instance(n, xy, w, depth, gbase, a.grid_x, [&](uint32_t t, unsigned long long word) {
-      a.pairs[atomicAdd(a.tile_cursor + (size_t)t * CNT_STRIDE, 1u)] = word; // absolute cursors
+      a.pairs[atomicAdd(a.tile_cursor + (size_t)t * CNT_STRIDE, 1u)] = word;
     });
-    if (tid == 0) stamp_done(a.prof, ST_DUP);
   }
+  if (tid == 0) stamp_done(a.prof, ST_DUP);
 }
 
 // ---- per-tile sort --------------------------------------------------------------------
@@ -482,22 +446,26 @@ __global__ void __launch_bounds__(1024) point_offsets_kernel(int P, const uint32
 
 cudaError_t launch_binning(const BinArgs& a, cudaStream_t s) {
   if (a.P <= 0 || a.num_tiles <= 0) return cudaSuccess;
-  static const cudaError_t optin = cudaFuncSetAttribute(duplicate_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  static const cudaError_t optin = cudaFuncSetAttribute(duplicate_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                         HIST_SMEM_MAX_TILES * (int)sizeof(uint32_t));
   if (optin != cudaSuccess) return optin;
-  const int dup_blocks = (a.P + DUP_THREADS - 1) / DUP_THREADS;
+  const int dup_blocks = (a.P + DUP_THREADS - 1) / DUP_THREADS + 1; // + the service CTA
+  const size_t hist = (size_t)a.num_tiles * sizeof(uint32_t);
   cudaError_t e;
-  if (a.num_tiles <= HIST_SMEM_MAX_TILES) {
-    e = launch_after(duplicate_kernel<true>, dim3(dup_blocks + 1), dim3(DUP_THREADS), (size_t)a.num_tiles * sizeof(uint32_t), s, a);
-    count_launch();
-  } else {
-    e = launch_after(tile_scan_kernel, dim3(1), dim3(DUP_THREADS), 0, s, a);
-    if (e == cudaSuccess) e = launch_after(duplicate_kernel<false>, dim3(dup_blocks), dim3(DUP_THREADS), 0, s, a);
+  if (a.num_tiles <= SCAN_IN_DUP_MAX_TILES) {
     count_launch(2);
+    e = launch_after(duplicate_kernel<true, true>, dim3(dup_blocks), dim3(DUP_THREADS), hist, s, a);
+  } else {
+    count_launch(3);
+    e = launch_after(tile_scan_kernel, dim3(1), dim3(DUP_THREADS), 0, s, a);
+    if (e != cudaSuccess) return e;
+    if (a.num_tiles <= HIST_SMEM_MAX_TILES)
+      e = launch_after(duplicate_kernel<true, false>, dim3(dup_blocks), dim3(DUP_THREADS), hist, s, a);
+    else
+      e = launch_after(duplicate_kernel<false, false>, dim3(dup_blocks), dim3(DUP_THREADS), 0, s, a);
   }
-  if (e == cudaSuccess) e = launch_after(tile_sort_kernel, dim3(a.num_tiles), dim3(TS_THREADS), 0, s, a);
-  count_launch();
-  return e;
+  if (e != cudaSuccess) return e;
+  return launch_after(tile_sort_kernel, dim3(a.num_tiles), dim3(TS_THREADS), 0, s, a);
 }
 
 void launch_point_offsets(int P, const uint32_t* tiles_touched, uint32_t* point_offsets, cudaStream_t s) {

@@ -4,6 +4,18 @@
 
 namespace igs {
 
+// what the tile scan (igs_tile_scan.cuh) reads and writes
+struct TileScanArgs {
+  int num_tiles;
+  int64_t capacity;
+  CtrlHeader* header;
+  int32_t* num_rendered_host; // device view of the caller's pinned slot (NULL: the host copies it)
+  uint32_t* info;             // [4] in the img workspace: {num_rendered, ...}, stays with the frame's state
+  const uint32_t* tile_count; // [T*CNT_STRIDE]
+  uint32_t* tile_cursor;      // [T*CNT_STRIDE] <- segment starts (when the duplicate CTAs do not scan themselves)
+  uint2* ranges;              // [T] [start, end) of each tile in the sorted list, (0,0) if empty
+};
+
 struct PreArgs {
   Prof prof;
   int P, D, M, ED, W, H, grid_x, grid_y, prefiltered;
@@ -21,18 +33,17 @@ struct PreArgs {
 
 struct BinArgs {
   Prof prof;
+  TileScanArgs scan;
   int P, grid_x, grid_y, num_tiles;
   int64_t capacity;
   const int32_t* radii;
   const float4* splat;
   const uint32_t* tiles_touched;
   CtrlHeader* header;
-  int32_t* num_rendered_host; // device view of the caller's pinned slot (NULL: the host copies it)
-  uint32_t* info;             // [4] in the img workspace: {num_rendered, ...}, stays with the frame's state
   uint32_t* tile_count;       // [T*CNT_STRIDE] instances per tile, from the preprocess kernel
-  uint32_t* tile_cursor;      // [T*CNT_STRIDE] slots handed out so far in each tile's segment (relative; absolute
-                              // when the counts do not fit shared memory, see tile_scan_kernel)
-  uint2* ranges;              // [T] [start, end) of each tile in the sorted list, (0,0) if empty
+  uint32_t* tile_cursor;      // [T*CNT_STRIDE] slots handed out in each tile's segment: relative to the segment start
+                              // when the duplicate CTAs scan the counts themselves, else absolute (tile_scan_kernel)
+  const uint2* ranges;        // [T] [start, end) of each tile in the sorted list, (0,0) if empty
   uint32_t* tile_order;       // [T] tile ids, longest list first (the render kernels' unit order)
   unsigned long long* pairs;  // [capacity] (depth bits << 32 | gaussian id), grouped by tile, unordered inside
   unsigned long long* pairs2; // [capacity] scratch of the two-level sort of segments beyond TS_CAP

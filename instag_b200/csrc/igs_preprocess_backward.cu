@@ -125,8 +125,14 @@ __device__ __forceinline__ float3 sh_backward(int deg, int M, const float* __res
   return dd;
 }
 
+// Resident CTAs per SM the register allocation aims at.  3 (80 registers, a few spills): the kernel
+// waits on its loads two thirds of the time, and 24 warps hide more of that than 16 (C5: 172.5 -> 164.3 us,
+// C2 10.6 -> 8.5); 4 CTAs (64 registers) spill too much (184.3).
+#ifndef IGS_PBW_MIN_CTAS
+#define IGS_PBW_MIN_CTAS 3
+#endif
 template <bool USE_SH>
-__global__ void __launch_bounds__(256) preprocess_backward_kernel(BwdPreArgs a) {
+__global__ void __launch_bounds__(256, IGS_PBW_MIN_CTAS) preprocess_backward_kernel(BwdPreArgs a) {
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   const int tid = threadIdx.x;
   if (a.prof.early) pdl_launch_dependents();

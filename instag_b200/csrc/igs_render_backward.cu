@@ -216,6 +216,10 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
         wh[i] = tf32_hi(wv[i]); wl[i] = __float_as_uint(wv[i] - __uint_as_float(wh[i]));
         gh[i] = tf32_hi(gv[i]); gl[i] = __float_as_uint(gv[i] - __uint_as_float(gh[i]));
       }
+      // (Measured and dropped: a third TF32 term for g -- hi + mid + lo carry all 24 bits.  The moments
+      // are shifted to the splat centre afterwards, which multiplies their rounding error by
+      // (distance / block size)^2: with two terms a splat ~300 px wide shows 2.4e-4 against the reference
+      // in dL_dcov3D, with three 5e-5; splats of a head are a few px wide, and the term costs 5 us.)
 #pragma unroll
       for (int h = 0; h < 2; h++) {
         const int b = 2 * h, o = 4 * h;

@@ -406,6 +406,8 @@ def main():
             return None
         return (c3_pair if a.workload == "C3" else face_pair)(a, torch, dist, device, local)
     if world > 1 and a.impl == "igs":
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"  # (NCCL prints its version on stdout, where the ONE JSON line goes)
         dist.init_process_group("nccl", device_id=device)
     eff_world = world if a.impl == "igs" else 1
 

@@ -283,8 +283,8 @@ int igs_densify_stats(int32_t P, const int32_t* radii, const float* grad_means2D
  * per-Gaussian gradient block (the reference has no multi-GPU path: north star).
  *   multicast_ptr       : the MULTICAST address of the buffer (same offset on every rank)
  *   signal_pad_ptrs_dev : device array of `world` pointers to the ranks' signal pads (zeroed;
- *                         signal_pad_bytes each, of which the bytes from 1024 on are used: one
- *                         4-byte flag per (CTA, peer), so the pad size bounds the CTA count)
+ *                         signal_pad_bytes each, of which world + 2 words from byte 1024 on are used:
+ *                         one flag per peer, two words for the rank's own CTAs)
  * as handed out by torch.distributed._symmetric_memory (multicast_ptr, signal_pad_ptrs_dev);
  * every rank must call it with the same n_floats on its own stream (instag_b200/sharding.py). */
 int igs_allreduce_nvls(void* multicast_ptr, void* signal_pad_ptrs_dev, int32_t signal_pad_bytes,

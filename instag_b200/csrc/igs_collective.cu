@@ -11,9 +11,13 @@
 //      fetch that 16-byte word from all replicas and return the sum, `multimem.st.v4.f32`
 //      broadcasts the sum back into all replicas -- each GPU moves 1/world of the block twice;
 //   3. barrier (all slices have landed everywhere).
-// The barriers are flag exchanges through the peers' signal pads: block b of rank r sets slot
-// [b][r] of every peer's pad from 0 to 1 (release, system scope) and waits until its own pad's
-// slots [b][*] are 1, resetting them to 0 (acquire) -- no epoch counters, reusable immediately.
+// The barriers are flag exchanges through the peers' signal pads: thread `peer` of CTA 0 of rank r
+// sets slot [r] of the peer's pad from 0 to 1 (release, system scope) and waits until slot [peer] of
+// its own pad is 1, resetting it to 0 (acquire) -- no epoch counters, reusable immediately.  Only CTA 0
+// talks to the peers; the other CTAs of the grid (all co-resident: at most one per SM) are released by,
+// and report to, CTA 0 through two words of the rank's own pad.  (r01: one flag per (CTA, peer), which
+// capped the grid at 24 CTAs -- too few 16-byte round trips in flight to cover the NVLink latency.)
+// The kernel is launched as a programmatic dependent of the per-Gaussian backward kernel that fills the block.
 #include <cstdlib>
 #include "igs_common.cuh"
 #include "igs_kernels.cuh"
@@ -21,9 +25,13 @@
 namespace igs {
 
 constexpr int AR_THREADS = 256;
-constexpr int AR_UNROLL = 4;
-constexpr int AR_MAX_BLOCKS = 24;   // signal-pad slots used: [AR_PAD_OFFSET + b * world + peer]
+#ifndef IGS_AR_UNROLL
+#define IGS_AR_UNROLL 4
+#endif
+constexpr int AR_UNROLL = IGS_AR_UNROLL;
+constexpr int AR_MAX_BLOCKS = 132;  // co-resident by construction (< 148 SMs)
 constexpr int AR_PAD_OFFSET = 256;  // in uint32 words: the first KB of the pad is left to torch's own barriers
+// words behind AR_PAD_OFFSET: [0, world) peer flags | [world] go | [world + 1] arrived
 
 __device__ __forceinline__ void put_flag(uint32_t* addr) {
   uint32_t old;
@@ -37,26 +45,44 @@ __device__ __forceinline__ void take_flag(uint32_t* addr) {
     asm volatile("atom.global.acquire.sys.cas.b32 %0, [%1], 1, 0;" : "=r"(old) : "l"(addr) : "memory");
   } while (old != 1u);
 }
+__device__ __forceinline__ uint32_t load_acquire(const uint32_t* addr) {
+  uint32_t v;
+  asm volatile("ld.global.acquire.gpu.b32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void store_release(uint32_t* addr, uint32_t v) {
+  asm volatile("st.global.release.gpu.b32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
 
-// all threads of the block arrive; thread t < world talks to peer t
+// CTA 0, all threads arrive; thread t < world talks to peer t
 __device__ __forceinline__ void rank_barrier(uint32_t* const* pads, int rank, int world) {
   __syncthreads();
   if ((int)threadIdx.x < world) {
     const int peer = threadIdx.x;
-    const size_t slot = AR_PAD_OFFSET + (size_t)blockIdx.x * world;
-    put_flag(pads[peer] + slot + rank);   // "block b of `rank` is here", in peer's pad
-    take_flag(pads[rank] + slot + peer);  // wait for block b of `peer`
+    put_flag(pads[peer] + AR_PAD_OFFSET + rank);   // "`rank` is here", in peer's pad
+    take_flag(pads[rank] + AR_PAD_OFFSET + peer);  // wait for `peer`
   }
   __syncthreads();
 }
 
 __global__ void __launch_bounds__(AR_THREADS) nvls_allreduce_kernel(float* mc, uint32_t* const* pads, int rank, int world,
                                                                     size_t n_vec4) {
-  rank_barrier(pads, rank, world);
-  // this rank's slice of 16-byte words, spread over the blocks
+  pdl_wait(); // this rank's gradient block is complete
+  uint32_t* const go = pads[rank] + AR_PAD_OFFSET + world;
+  uint32_t* const arrived = go + 1;
+  // 1. every rank's block is complete: CTA 0 meets the peers, then releases the local CTAs
+  if (blockIdx.x == 0) {
+    rank_barrier(pads, rank, world);
+    if (threadIdx.x == 0) store_release(go, 1u);
+  } else {
+    if (threadIdx.x == 0)
+      while (load_acquire(go) == 0u) {}
+    __syncthreads();
+  }
+  // 2. this rank's slice of 16-byte words, spread over the CTAs; AR_UNROLL independent switch round
+  //    trips in flight per thread
   const size_t per = (n_vec4 + world - 1) / world;
   const size_t lo = min(n_vec4, per * rank), hi = min(n_vec4, lo + per);
-  // AR_UNROLL independent switch round trips in flight per thread
   const size_t stride = (size_t)gridDim.x * AR_THREADS;
   for (size_t i = lo + (size_t)blockIdx.x * AR_THREADS + threadIdx.x; i < hi; i += stride * AR_UNROLL) {
     float4 v[AR_UNROLL];
@@ -71,7 +97,19 @@ __global__ void __launch_bounds__(AR_THREADS) nvls_allreduce_kernel(float* mc, u
         asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
                      ::"l"(mc + 4 * (i + u * stride)), "f"(v[u].x), "f"(v[u].y), "f"(v[u].z), "f"(v[u].w) : "memory");
   }
+  // 3. all slices have landed everywhere: the local CTAs report to CTA 0, CTA 0 meets the peers again
   __threadfence_system();
+  __syncthreads();
+  if (blockIdx.x != 0) {
+    if (threadIdx.x == 0) atomicAdd(arrived, 1u);
+    return;
+  }
+  if (threadIdx.x == 0) {
+    while (load_acquire(arrived) != gridDim.x - 1) {}
+    *arrived = 0u; // the two words go back to zero for the next call (stream order: it starts after this one ends)
+    *go = 0u;
+    __threadfence();
+  }
   rank_barrier(pads, rank, world);
 }
 
@@ -83,9 +121,6 @@ extern "C" {
 
 int igs_allreduce_nvls(void* multicast_ptr, void* signal_pad_ptrs_dev, int32_t signal_pad_bytes, int32_t rank,
                        int32_t world, int64_t n_floats, igs_stream_t stream) {
-  // blocks are limited by the flag slots the pad has behind AR_PAD_OFFSET: one per (block, peer)
-  const int max_blocks_arg = signal_pad_bytes > 0 ? (signal_pad_bytes / 4 - AR_PAD_OFFSET) / (world > 0 ? world : 1) : 0;
-  if (signal_pad_bytes > 0 && max_blocks_arg < 1) { set_error("allreduce_nvls: signal pad too small"); return IGS_ERR_INVALID; }
   if (!multicast_ptr || !signal_pad_ptrs_dev || world < 1 || world > 32 || rank < 0 || rank >= world || n_floats < 0 ||
       (n_floats & 3) || ((uintptr_t)multicast_ptr & 15)) {
     set_error("allreduce_nvls: bad arguments (n_floats must be a multiple of 4, the pointer 16-byte aligned)");
@@ -93,13 +128,23 @@ int igs_allreduce_nvls(void* multicast_ptr, void* signal_pad_ptrs_dev, int32_t s
   }
   if (n_floats == 0 || world == 1) return IGS_OK;
   const size_t n4 = (size_t)n_floats / 4, per = (n4 + world - 1) / world;
-  static const int vpt = [] { const char* e = getenv("IGS_AR_VPT"); const int v = e ? atoi(e) : 8; return v < 1 ? 1 : v; }();
-  int blocks = (int)((per + AR_THREADS * vpt - 1) / (AR_THREADS * vpt)); // 16-byte words per thread (tuning: IGS_AR_VPT)
-  const int max_blocks = max_blocks_arg > 0 ? max_blocks_arg : AR_MAX_BLOCKS;
+  if (signal_pad_bytes > 0 && (size_t)signal_pad_bytes < (AR_PAD_OFFSET + (size_t)world + 2) * 4) {
+    set_error("allreduce_nvls: signal pad too small"); return IGS_ERR_INVALID;
+  }
+  // enough CTAs that one sweep of AR_UNROLL 16-byte words per thread covers the slice, at most one per SM
+  static const int max_blocks = [] {
+    const char* e = getenv("IGS_AR_BLOCKS");
+    int v = e ? atoi(e) : AR_MAX_BLOCKS, sms = 0, dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms > 16 && v > sms - 16) v = sms - 16; // (co-residency is what the local release / report relies on)
+    return v < 1 ? 1 : v;
+  }();
+  int blocks = (int)((per + AR_THREADS * AR_UNROLL - 1) / (AR_THREADS * AR_UNROLL));
   blocks = blocks < 1 ? 1 : blocks > max_blocks ? max_blocks : blocks;
-  nvls_allreduce_kernel<<<blocks, AR_THREADS, 0, (cudaStream_t)stream>>>((float*)multicast_ptr,
-                                                                          (uint32_t* const*)signal_pad_ptrs_dev, rank,
-                                                                          world, n4);
+  if (int r = check_cuda(launch_after(nvls_allreduce_kernel, dim3(blocks), dim3(AR_THREADS), 0, (cudaStream_t)stream,
+                                      (float*)multicast_ptr, (uint32_t* const*)signal_pad_ptrs_dev, (int)rank, (int)world, n4),
+                         "allreduce_nvls launch")) return r;
   count_launch();
   return stage_check(false, (cudaStream_t)stream, "allreduce_nvls");
 }

@@ -1053,6 +1053,15 @@ def adjacent_kernels(torch, device, flush, reps=20):
             run("l1_ssim_forward" + tag, lambda: LS.l1_ssim_loss(img, gt), 3 * side * side * 4 * (2 + 3))
         loss = LS.l1_ssim_loss(img, gt)
         run("l1_ssim_backward" + tag, lambda: torch.autograd.grad(loss, img, retain_graph=True), 3 * side * side * 4 * (5 + 1))
+        dep, alp = rnd(1, side, side).requires_grad_(True), rnd(1, side, side).requires_grad_(True)
+        nrm, ngt, dmo = rnd(3, side, side).requires_grad_(True), rnd(3, side, side), rnd(side, side)
+        hm, fm, mm = rnd(side, side) < 0.7, rnd(side, side) < 0.5, rnd(side, side) < 0.1
+        with torch.no_grad():
+            run("geometry_losses_forward" + tag, lambda: LS.geometry_losses(dep, nrm, alp, dmo, ngt, hm, fm, mm),
+                side * side * (4 * 11 + 3 + 4 * 2 + 2))
+        gl, _ = LS.geometry_losses(dep, nrm, alp, dmo, ngt, hm, fm, mm)
+        run("geometry_losses_backward" + tag, lambda: torch.autograd.grad(gl, (dep, nrm, alp), retain_graph=True),
+            side * side * (4 * 5 + 3 + 4 * 5))
     out["note"] = ("host wrappers included (one autograd.Function call per launch; l1_ssim_forward also sums its "
                    "per-CTA partials with torch); *_large = 2048^2 frame / 4M Gaussians")
     return out

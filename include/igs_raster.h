@@ -306,6 +306,28 @@ int igs_l1_ssim_backward(const float* img1, const float* img2, const float* dA, 
                          const float* dC, int32_t C, int32_t H, int32_t W, float lambda_dssim,
                          const float* grad_out, float* grad_img1, igs_stream_t stream);
 
+/* f3 (the rest)  igs_geom_loss_* replace the geometry regularisers train_face.py computes on the
+ *     rasterizer's depth / normal / alpha images (/root/reference/train_face.py:469, :481-491 with
+ *     utils/loss_utils.py:17-20 `normalize`, :540):
+ *         l_normal = w_normal * (1 - normal_gt * normal).sum(0)[head ^ mouth].mean()
+ *         l_depth  = w_depth  * (normalize(depth[0])[face ^ mouth] - normalize(depth_mono)[face ^ mouth]).abs().mean()
+ *         l_alpha  = w_alpha  * (((1 - alpha) * head).mean() + (alpha * ~head).mean())
+ *     (the reference's weights: 0.01, 1e-2, 1e-3; a weight of 0 switches a term off) and their autograd
+ *     backward, which yields the dL_ddepth [1,H,W], dL_dnorm [3,H,W], dL_dalpha [1,H,W] images igs_backward
+ *     consumes.  depth, alpha [1,H,W]; norm, normal_gt [3,H,W]; depth_mono [H,W]; masks [H,W] bytes
+ *     (torch.bool).  workspace: igs_geom_loss_workspace(H) bytes, 8-byte aligned, kept for backward.
+ *     forward : loss3 <- {l_normal, l_depth, l_alpha} (device).
+ *     backward: gradients of *grad_out * (l_normal + l_depth + l_alpha) (grad_out: device scalar). */
+size_t igs_geom_loss_workspace(int32_t H);
+int igs_geom_loss_forward(const float* depth, const float* norm, const float* alpha, const float* depth_mono,
+                          const float* normal_gt, const uint8_t* head_mask, const uint8_t* face_mask,
+                          const uint8_t* mouth_mask, int32_t H, int32_t W, float w_normal, float w_depth, float w_alpha,
+                          void* workspace, float* loss3, igs_stream_t stream);
+int igs_geom_loss_backward(const float* depth, const float* depth_mono, const float* normal_gt, const uint8_t* head_mask,
+                           const uint8_t* face_mask, const uint8_t* mouth_mask, int32_t H, int32_t W, float w_normal,
+                           float w_depth, float w_alpha, const void* workspace, const float* grad_out, float* dL_ddepth,
+                           float* dL_dnorm, float* dL_dalpha, igs_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

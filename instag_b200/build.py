@@ -15,7 +15,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libigs_raster.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 SOURCES = ["igs_api.cu", "igs_preprocess.cu", "igs_binning.cu", "igs_render.cu",
-           "igs_render_backward.cu", "igs_preprocess_backward.cu", "igs_adjacent.cu", "igs_loss.cu", "igs_collective.cu"]
+           "igs_render_backward.cu", "igs_preprocess_backward.cu", "igs_adjacent.cu", "igs_loss.cu", "igs_geom_loss.cu", "igs_collective.cu"]
 # IGS_NVCC_DEFS="-DX=1 -DY=2": extra macro definitions for kernel experiments (profiles/ notes say which)
 FLAGS = os.environ.get("IGS_NVCC_DEFS", "").split() + ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
          "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]

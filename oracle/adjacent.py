@@ -141,3 +141,41 @@ def l1_ssim_loss(image, gt, lambda_dssim=0.2):
     dssim = _conv_same(A, win) + 2 * x * _conv_same(df_ds1, win) + y * _conv_same(df_ds12, win)
     grad = (np.sign(x - y) - lambda_dssim * dssim) / n
     return float(loss), float(l1), float(ssim), grad.astype(F32)
+
+
+def geometry_losses(depth, normal, alpha, depth_mono, normal_gt, head_mask, face_mask, mouth_mask):
+    """The geometry regularisers of train_face.py on the rasterizer's depth / normal / alpha images:
+        :469  0.01 * (1 - normal_gt * normal).sum(0)[head ^ mouth].mean()
+        :491  1e-2 * (normalize(depth)[face ^ mouth] - normalize(depth_mono)[face ^ mouth]).abs().mean()
+              normalize (utils/loss_utils.py:17-20): per ROW of the [H,W] map, (x - mean_row) /
+              (std_row + 1e-2 * std(all)), unbiased standard deviations
+        :540  1e-3 * (((1 - alpha) * head).mean() + (alpha * ~head).mean())
+    Returns ((l_normal, l_depth, l_alpha), (dL/ddepth [1,H,W], dL/dnormal [3,H,W], dL/dalpha [1,H,W])) of their
+    sum, float64 arithmetic, analytic adjoints."""
+    d, m = np.asarray(depth, np.float64)[0], np.asarray(depth_mono, np.float64)
+    n, ng, a = np.asarray(normal, np.float64), np.asarray(normal_gt, np.float64), np.asarray(alpha, np.float64)[0]
+    head, face, mouth = (np.asarray(x).astype(bool) for x in (head_mask, face_mask, mouth_mask))
+    H, W = d.shape
+    m1, m2 = head ^ mouth, face ^ mouth
+    l_normal = 0.01 * (3.0 - (ng * n).sum(0))[m1].mean()
+    g_normal = -0.01 * ng * m1[None] / m1.sum()
+
+    def stats(x):
+        mu = x.mean(1, keepdims=True)
+        sd = x.std(1, ddof=1, keepdims=True)
+        return mu, sd, x.mean(), x.std(ddof=1)
+    mu, sd, mu_g, sd_g = stats(d)
+    s = sd + 1e-2 * sd_g
+    z = (d - mu) / s
+    mu_m, sd_m, _, sd_gm = stats(m)
+    zm = (m - mu_m) / (sd_m + 1e-2 * sd_gm)
+    diff = z - zm
+    l_depth = 1e-2 * np.abs(diff[m2]).mean()
+    u = 1e-2 * np.sign(diff) * m2 / m2.sum()                         # dL/dz
+    A = u.sum(1, keepdims=True)
+    B = (u * (d - mu)).sum(1, keepdims=True) / (s * s)               # = sum_i u_i (x_i - mu_r) / s_r^2
+    g_depth = u / s - A / (W * s) - B * (d - mu) / ((W - 1) * sd) - 1e-2 * B.sum() * (d - mu_g) / ((H * W - 1) * sd_g)
+    l_alpha = 1e-3 * (((1 - a) * head).mean() + (a * ~head).mean())
+    g_alpha = 1e-3 * np.where(head, -1.0, 1.0) / (H * W)
+    return (float(l_normal), float(l_depth), float(l_alpha)), \
+        (g_depth[None].astype(F32), g_normal.astype(F32), g_alpha[None].astype(F32))

@@ -92,7 +92,38 @@ def loss_case(H, W, seed, lam=0.2):
                 l1=Ll1.detach().numpy(), ssim=ssim(image.detach(), gt).numpy(), grad_x3=image.grad.numpy())
 
 
+def geometry_case(H, W, seed):
+    """train_face.py:469 (normal), :481-491 (depth, with the reference's own utils/loss_utils.normalize)
+    and :540 (alpha), on rasterizer-shaped outputs; gradients by torch autograd."""
+    import sys
+    sys.path.insert(0, "/root/reference")
+    from utils.loss_utils import normalize  # utils/loss_utils.py:17-20
+    g = torch.Generator().manual_seed(seed)
+    depth_img = (torch.rand((1, H, W), generator=g) * 0.9).requires_grad_(True)
+    normal_img = F.normalize(torch.randn((3, H, W), generator=g), dim=0).requires_grad_(True)
+    alpha_img = torch.rand((1, H, W), generator=g).requires_grad_(True)
+    depth_mono = torch.rand((H, W), generator=g)
+    normal_gt = F.normalize(torch.randn((3, H, W), generator=g), dim=0)
+    yy, xx = torch.meshgrid(torch.arange(H), torch.arange(W), indexing="ij")
+    r2 = ((yy - H / 2) / (H / 2)) ** 2 + ((xx - W / 2) / (W / 2)) ** 2
+    head_mask, face_mask = r2 < 0.8, r2 < 0.5
+    mouth_mask = (((yy - 0.7 * H) / (0.1 * H)) ** 2 + ((xx - W / 2) / (0.2 * W)) ** 2) < 1.0
+    render_pkg = {"normal": normal_img, "depth": depth_img}
+    alpha = alpha_img
+    l_normal = 0.01 * (1 - normal_gt * render_pkg["normal"]).sum(0)[head_mask ^ mouth_mask].mean()      # train_face.py:469
+    depth = render_pkg["depth"][0]                                                                      # :481
+    l_depth = 1e-2 * (normalize(depth)[face_mask ^ mouth_mask] - normalize(depth_mono)[face_mask ^ mouth_mask]).abs().mean()  # :491
+    l_alpha = 1e-3 * (((1 - alpha) * head_mask).mean() + (alpha * ~head_mask).mean())                    # :540
+    (2.0 * (l_normal + l_depth + l_alpha)).backward()
+    return dict(depth=depth_img.detach().numpy(), normal=normal_img.detach().numpy(), alpha=alpha_img.detach().numpy(),
+                depth_mono=depth_mono.numpy(), normal_gt=normal_gt.numpy(), head_mask=head_mask.numpy(),
+                face_mask=face_mask.numpy(), mouth_mask=mouth_mask.numpy(), l_normal=l_normal.detach().numpy(),
+                l_depth=l_depth.detach().numpy(), l_alpha=l_alpha.detach().numpy(), g_depth_x2=depth_img.grad.numpy(),
+                g_normal_x2=normal_img.grad.numpy(), g_alpha_x2=alpha_img.grad.numpy())
+
+
 if __name__ == "__main__":
+    np.savez_compressed(os.path.join(HERE, "adjacent_geometry.npz"), **geometry_case(52, 44, 6))
     np.savez_compressed(os.path.join(HERE, "adjacent_loss.npz"), **loss_case(45, 61, 5))
     np.savez_compressed(os.path.join(HERE, "adjacent_compose_plain.npz"), **compose_case(37, 53, 1, False))
     np.savez_compressed(os.path.join(HERE, "adjacent_compose_dilate.npz"), **compose_case(48, 40, 2, True))

@@ -67,3 +67,12 @@ def test_l1_ssim_loss_matches_the_references_loss_utils():
     loss, l1, ss, grad = A.l1_ssim_loss(g["image"], g["gt"], float(g["lam"]))
     assert abs(loss - float(g["loss"])) <= 1e-6 and abs(l1 - float(g["l1"])) <= 1e-6 and abs(ss - float(g["ssim"])) <= 1e-6
     assert np.abs(3 * grad - g["grad_x3"]).max() <= 1e-5 * np.abs(g["grad_x3"]).max()
+
+
+def test_geometry_losses_match_train_face_expressions():
+    g = _load("adjacent_geometry.npz")  # train_face.py:469,491,540 with the reference's own normalize()
+    (ln, ld, la), (gd, gn, ga) = A.geometry_losses(g["depth"], g["normal"], g["alpha"], g["depth_mono"], g["normal_gt"],
+                                                   g["head_mask"], g["face_mask"], g["mouth_mask"])
+    assert abs(ln - float(g["l_normal"])) <= 1e-7 and abs(ld - float(g["l_depth"])) <= 1e-7 and abs(la - float(g["l_alpha"])) <= 1e-8
+    for a, b in ((2 * gd, g["g_depth_x2"]), (2 * gn, g["g_normal_x2"]), (2 * ga, g["g_alpha_x2"])):
+        assert np.abs(a - b).max() <= 2e-5 * np.abs(b).max()

@@ -256,6 +256,77 @@ def _torch_ssim(img1, img2):
     return (((2 * mu1 * mu2 + C1) * (2 * s12 + C2)) / ((mu1.pow(2) + mu2.pow(2) + C1) * (s1 + s2 + C2))).mean()
 
 
+def _torch_normalize(x):  # utils/loss_utils.py:17-20
+    import torch
+    return (x - torch.mean(x, dim=1, keepdim=True)) / (torch.std(x, dim=1, keepdim=True) + 1e-2 * torch.std(x.reshape(-1)))
+
+
+def test_geometry_losses_match_golden_oracle_and_feed_the_rasterizer_backward():
+    """f3, the rest: the normal / depth / alpha regularisers of train_face.py:469,491,540.  (a) the golden
+    made from the reference's expressions, (b) the numpy oracle on a ragged size, (c) the whole chain
+    rasterizer -> losses -> dL_ddepth / dL_dnorm / dL_dalpha -> per-Gaussian gradients against the same
+    chain written with the reference's torch expressions."""
+    import torch
+    from diff_gauss import GaussianRasterizer
+    from instag_b200 import losses as LS
+    g = dict(np.load(os.path.join(G, "adjacent_geometry.npz")))
+    leaves = [_t(g[k]).requires_grad_(True) for k in ("depth", "normal", "alpha")]
+    total, terms = LS.geometry_losses(*leaves, _t(g["depth_mono"]), _t(g["normal_gt"]), _t(g["head_mask"]),
+                                      _t(g["face_mask"]), _t(g["mouth_mask"]))
+    (2.0 * total).backward()
+    want = [float(g[k]) for k in ("l_normal", "l_depth", "l_alpha")]
+    assert np.abs(terms.cpu().numpy() - want).max() <= 2e-7
+    for leaf, key in zip(leaves, ("g_depth_x2", "g_normal_x2", "g_alpha_x2")):
+        assert np.abs(leaf.grad.cpu().numpy() - g[key]).max() <= 3e-5 * np.abs(g[key]).max(), key
+    # (b) ragged size, against the oracle; a switched-off term contributes nothing
+    rng = np.random.default_rng(5)
+    H, W = 37, 301
+    d, a = rng.random((1, H, W), dtype=np.float32), rng.random((1, H, W), dtype=np.float32)
+    n, ng = rng.standard_normal((3, H, W)).astype(np.float32), rng.standard_normal((3, H, W)).astype(np.float32)
+    dm = rng.random((H, W), dtype=np.float32)
+    hm, fm, mm = rng.random((H, W)) < 0.7, rng.random((H, W)) < 0.5, rng.random((H, W)) < 0.1
+    (ln, ld, la), (gd, gn, ga) = A.geometry_losses(d, n, a, dm, ng, hm, fm, mm)
+    lv = [_t(x).requires_grad_(True) for x in (d, n, a)]
+    total, terms = LS.geometry_losses(*lv, _t(dm), _t(ng), _t(hm), _t(fm), _t(mm))
+    total.backward()
+    assert np.abs(terms.cpu().numpy() - [ln, ld, la]).max() <= 2e-7
+    for leaf, w in zip(lv, (gd, gn, ga)):
+        assert np.abs(leaf.grad.cpu().numpy() - w).max() <= 3e-5 * np.abs(w).max()
+    _, off = LS.geometry_losses(*[x.detach() for x in lv], _t(dm), _t(ng), _t(hm), _t(fm), _t(mm), w_depth=0.0)
+    assert float(off[1]) == 0.0 and abs(float(off[0]) - ln) <= 2e-7
+    # (c) the chain through the rasterizer
+    sc = U.make_scene(P=4000, W=96, H=80, sh_degree=None, ED=1, scale_mult=2.0, seed=33)
+    t = U.to_torch(sc)
+    gen = torch.Generator("cuda").manual_seed(2)
+    depth_mono = torch.rand((80, 96), device="cuda", generator=gen)
+    normal_gt = torch.nn.functional.normalize(torch.randn((3, 80, 96), device="cuda", generator=gen), dim=0)
+    yy, xx = torch.meshgrid(torch.arange(80, device="cuda"), torch.arange(96, device="cuda"), indexing="ij")
+    head_mask, face_mask = (yy - 40) ** 2 + (xx - 48) ** 2 < 38 ** 2, (yy - 40) ** 2 + (xx - 48) ** 2 < 25 ** 2
+    mouth_mask = ((yy - 55) ** 2 * 4 + (xx - 48) ** 2) < 12 ** 2
+
+    def run(fused):
+        m3 = t["means3D"].clone().requires_grad_(True)
+        op = t["opacities"].clone().requires_grad_(True)
+        rot = t["rotations"].clone().requires_grad_(True)
+        image, depth, normal, alpha, radii, extra = GaussianRasterizer(U.settings_from(t))(
+            means3D=m3, means2D=torch.zeros_like(m3), colors_precomp=t["colors_precomp"], opacities=op,
+            scales=t["scales"], rotations=rot, extra_attrs=t["extra_attrs"])
+        if fused:
+            loss, _ = LS.geometry_losses(depth, normal, alpha, depth_mono, normal_gt, head_mask, face_mask, mouth_mask)
+        else:
+            loss = 0.01 * (1 - normal_gt * normal).sum(0)[head_mask ^ mouth_mask].mean()                       # train_face.py:469
+            loss = loss + 1e-2 * (_torch_normalize(depth[0])[face_mask ^ mouth_mask] -
+                                  _torch_normalize(depth_mono)[face_mask ^ mouth_mask]).abs().mean()               # :491
+            loss = loss + 1e-3 * (((1 - alpha) * head_mask).mean() + (alpha * ~head_mask).mean())                 # :540
+        loss.backward()
+        return float(loss), m3.grad, op.grad, rot.grad
+
+    a_, b_ = run(True), run(False)
+    assert abs(a_[0] - b_[0]) <= 2e-6
+    for x, y in zip(a_[1:], b_[1:]):
+        assert float((x - y).abs().max()) <= 3e-4 * float(y.abs().max())
+
+
 def test_deferred_counts_give_the_same_frames_and_repair_a_frame_that_was_cut_short():
     """DeferredCounts: the no-grad calls of the sequence do not wait for num_rendered.  The splats
     grow 3x in the middle of the sequence, so the instance count of that frame exceeds the

@@ -229,9 +229,10 @@ int igs_profile_enable(int on);
 int igs_profile_read(float* ms /* [IGS_NUM_STAGES] */, int32_t* frames);
 uint64_t igs_launch_count(void);
 
-/* Debug hook: with a non-NULL device buffer of 3*8*T uint64 words the forward render kernel records,
- * per (tile, 8x4 block) unit, {globaltimer at start, at end, smid | list length << 32}; NULL switches
- * it off.  Used by scratch/trace_units.py to look at the load balance; not part of the reference API. */
+/* Debug hook: with a non-NULL device buffer of 4*8*T uint64 words the forward render kernel records,
+ * per (tile, 8x4 block) unit, {globaltimer at start, at end, smid | list length << 32, chunks of 32
+ * entries walked | entries that survived the cull << 32}; NULL switches it off.  Used by
+ * profiles/tools/trace_units.py to look at the load balance; not part of the reference API. */
 int igs_debug_trace(void* device_buffer);
 
 int igs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,

@@ -137,6 +137,7 @@ __global__ void __launch_bounds__(RT, 6) render_kernel(RenderArgs a) {
   copies_commit();
   uint32_t par = 0; // which r2 / r3 buffer the current chunk reads
 
+  uint32_t tr_chunks = 0, tr_surv = 0; // (trace only)
   for (int cb = 0; cb < total; cb += 32) {
     if (__all_sync(0xffffffffu, done)) break;
     const bool live = cb + lane < total;
@@ -144,6 +145,7 @@ __global__ void __launch_bounds__(RT, 6) render_kernel(RenderArgs a) {
     const bool hit = live && splat_may_touch(q0.x, q0.y, q0.z, q1.x, q1.y, 2.f * __logf(255.f * q0.w),
                                              wx0, wx1, wy0, wy1);
     unsigned m = __ballot_sync(0xffffffffu, hit);
+    if (trace) { tr_chunks++; tr_surv += __popc(m); }
     const uint32_t id_mine = id_cur;
     const float4 c0 = q0, c1 = q1;
     // this chunk's r2 / r3 planes have landed; everybody is done reading the previous chunk's slots
@@ -257,8 +259,9 @@ __global__ void __launch_bounds__(RT, 6) render_kernel(RenderArgs a) {
   copies_wait(); // (a unit that stopped early leaves its last prefetch in flight)
   __syncwarp();  // the next unit reuses this warp's shared-memory slots
   if (trace && lane == 0) {
-    trace[3 * unit] = t_start; trace[3 * unit + 1] = gtimer();
-    trace[3 * unit + 2] = (unsigned long long)smid() | ((unsigned long long)total << 32);
+    trace[4 * unit] = t_start; trace[4 * unit + 1] = gtimer();
+    trace[4 * unit + 2] = (unsigned long long)smid() | ((unsigned long long)total << 32);
+    trace[4 * unit + 3] = (unsigned long long)tr_chunks | ((unsigned long long)tr_surv << 32);
   }
  } // unit loop
   if (lane == 0) stamp_done(a.prof, ST_RENDER);

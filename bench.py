@@ -286,13 +286,14 @@ class Arm:
 
     # ---- the same step recorded into CUDA graphs (igs arm only: the reference's forward blocks on a
     # cudaMemcpy of num_rendered, rasterizer_impl.cu:284, and cannot be recorded) ----
-    def build_graphs(self):
+    def build_graphs(self, after_backward=None):
         """Two graphs, one per input block: graph k = {H2D of the NEXT step's inputs into block k^1 on a
         forked stream} || {GaussianRasterizer(...) on block k -> loss -> backward -> loss D2H}.  Recorded
         through the public module API; a replay is one step with the same copies as step_e2e."""
         torch = self.torch
         side = torch.cuda.Stream(self.device)
         self.graph_stream = side
+        self.after_backward = after_backward  # e.g. the exchange step of a view-sharded batch, recorded with the step
         self.graphs, self.graph_keep = [], []
         side.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(side):
@@ -317,6 +318,8 @@ class Arm:
         with torch.cuda.stream(self.copy_stream):
             self.dev[k ^ 1].copy_(self.host, non_blocking=True)
         leaves = self.leaves[k]
+        for v in leaves.values():
+            v.grad = None
         m2 = torch.zeros_like(leaves["means3D"], requires_grad=True)
         color, depth, norm, alpha, radii, extra = self.Module(self.rs)(
             means3D=leaves["means3D"], means2D=m2, shs=leaves.get("shs"),
@@ -325,6 +328,8 @@ class Arm:
         outs = [color, depth, norm, alpha] + ([extra] if self.ED else [])
         loss = torch.dot(torch.cat([o.reshape(-1) for o in outs]), self.wflat)
         loss.backward()
+        if self.after_backward is not None:
+            self.after_backward(leaves)
         self.loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
         stream.wait_stream(self.copy_stream)  # join
         return leaves, m2, loss
@@ -513,16 +518,21 @@ def main():
                        "GaussianRasterizer(...) -> loss = <all heads, fixed weights> -> backward -> loss D2H"}
     else:
         e2e = {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
-    # the same step recorded once into CUDA graphs through the module API and replayed (one process per GPU,
-    # no collective inside the graph: N=1 only)
+    # the same step recorded once into CUDA graphs through the module API and replayed; with N > 1 the exchange
+    # step (igs_allreduce_nvls, one kernel) is recorded with it
     a.e2e_graph = None
-    if backward and not a.value_only and a.impl == "igs" and eff_world == 1 and not a.no_graph:
+    if backward and not a.value_only and a.impl == "igs" and (eff_world == 1 or block is not None) and not a.no_graph:
         try:
             from instag_b200 import rasterizer as R_
-            arm.build_graphs()
-            ms_g, _, _ = timed(torch, dist, arm.step_e2e_graph, a.steps, max(a.warmup, 3), flush, 1)
+
+            def exchange(leaves):
+                if not block.holds([v.grad for v in leaves.values()]):
+                    raise RuntimeError("the recorded gradients are not in the multicast block")
+                block.all_reduce()
+            arm.build_graphs(exchange if eff_world > 1 else None)
+            ms_g, _, _ = timed(torch, dist, arm.step_e2e_graph, a.steps, max(a.warmup, 3), flush, eff_world)
             over = bool(R_.binding().captured_overflowed())
-            a.e2e_graph = {"value": 1000.0 / ms_g, "unit": "frames/s", "ms_per_step": ms_g,
+            a.e2e_graph = {"value": eff_world * 1000.0 / ms_g, "unit": "frames/s", "ms_per_step": ms_g,
                            "h2d_bytes_per_step": arm.h2d_bytes, "d2h_bytes_per_step": 4,
                            "instance_workspaces_overflowed": over, "loss": float(arm.loss_host[0]),
                            "path": "the step of e2e (H2D of the next inputs on a forked stream, GaussianRasterizer(...), "

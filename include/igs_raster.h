@@ -303,6 +303,9 @@ int igs_allreduce_nvls(void* multicast_ptr, void* signal_pad_ptrs_dev, int32_t s
 size_t igs_l1_ssim_partials(int32_t C, int32_t H, int32_t W);
 int igs_l1_ssim_forward(const float* img1, const float* img2, int32_t C, int32_t H, int32_t W, float* dA,
                         float* dB, float* dC, float* partial, igs_stream_t stream);
+/*     finish  : out3 <- {loss = Ll1 + lambda_dssim * (1 - ssim), Ll1, ssim} from the partial sums (device). */
+int igs_l1_ssim_finish(const float* partial, int32_t C, int32_t H, int32_t W, float lambda_dssim, float* out3,
+                       igs_stream_t stream);
 int igs_l1_ssim_backward(const float* img1, const float* img2, const float* dA, const float* dB,
                          const float* dC, int32_t C, int32_t H, int32_t W, float lambda_dssim,
                          const float* grad_out, float* grad_img1, igs_stream_t stream);

@@ -154,11 +154,40 @@ __global__ void __launch_bounds__(LT * LT) l1_ssim_backward_kernel(
   grad_img1[pix] = __ldg(grad_out) * inv_n * (sgn - lambda_dssim * dssim);
 }
 
+// {loss, Ll1, ssim} from the forward kernel's per-CTA partial sums, in a fixed order (deterministic)
+__global__ void __launch_bounds__(256) l1_ssim_finish_kernel(const float* __restrict__ partial, int n, float inv_n,
+                                                             float lambda_dssim, float* __restrict__ out3) {
+  __shared__ double s_red[2][8];
+  double a = 0.0, b = 0.0;
+  for (int i = threadIdx.x; i < n; i += 256) { a += partial[2 * i]; b += partial[2 * i + 1]; }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+  if ((threadIdx.x & 31) == 0) { s_red[0][threadIdx.x >> 5] = a; s_red[1][threadIdx.x >> 5] = b; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    a = 0.0; b = 0.0;
+    for (int w = 0; w < 8; w++) { a += s_red[0][w]; b += s_red[1][w]; }
+    const float ssim = (float)(a * inv_n), l1 = (float)(b * inv_n);
+    out3[0] = l1 + lambda_dssim * (1.0f - ssim);
+    out3[1] = l1;
+    out3[2] = ssim;
+  }
+}
+
 } // namespace igs
 
 using namespace igs;
 
 extern "C" {
+
+int igs_l1_ssim_finish(const float* partial, int32_t C, int32_t H, int32_t W, float lambda_dssim, float* out3,
+                       igs_stream_t stream) {
+  if (C <= 0 || H <= 0 || W <= 0 || !partial || !out3) { set_error("l1_ssim finish: bad arguments"); return IGS_ERR_INVALID; }
+  const int n = (int)igs_l1_ssim_partials(C, H, W);
+  l1_ssim_finish_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(partial, n, 1.0f / ((float)C * (float)H * (float)W), lambda_dssim, out3);
+  count_launch();
+  return stage_check(false, (cudaStream_t)stream, "l1_ssim finish");
+}
 
 size_t igs_l1_ssim_partials(int32_t C, int32_t H, int32_t W) {
   return (size_t)(C > 0 ? C : 0) * ((H + LT - 1) / LT) * ((W + LT - 1) / LT);

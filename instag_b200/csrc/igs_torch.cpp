@@ -172,9 +172,13 @@ thread_local bool t_defer = false;
 thread_local int64_t t_serial = 0;                              // deferred calls so far on this thread
 thread_local std::deque<std::pair<int64_t, Pending>>* t_pending = nullptr;  // (serial, entry), oldest first
 
+// fp32, contiguous and 16-byte aligned (the kernels use vector accesses; a contiguous view at an odd
+// storage offset -- which the reference accepts -- is copied)
 inline Tensor f32c(const Tensor& t) {
   Tensor r = t.scalar_type() == at::kFloat ? t : t.to(at::kFloat);
-  return r.is_contiguous() ? r : r.contiguous();
+  if (!r.is_contiguous()) return r.contiguous();
+  if (r.numel() && (reinterpret_cast<uintptr_t>(r.data_ptr()) & 15u)) return r.clone();
+  return r;
 }
 inline const float* fptr(const Tensor& t) { return t.numel() ? t.data_ptr<float>() : nullptr; }
 inline float* fptr_mut(Tensor& t) { return t.numel() ? t.data_ptr<float>() : nullptr; }

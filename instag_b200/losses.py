@@ -33,11 +33,12 @@ class _L1SSIM(torch.autograd.Function):
             N.check(lib.igs_l1_ssim_forward(x.data_ptr(), y.data_ptr(), C_, H, W, maps[0].data_ptr(),
                                             maps[1].data_ptr(), maps[2].data_ptr(), part.data_ptr(), stream),
                     "l1_ssim forward")
-        sums = part.sum(dim=0) / float(C_ * H * W)          # [mean ssim, Ll1]
+            out3 = torch.empty((3,), dtype=torch.float32, device=x.device)   # loss, Ll1, mean ssim
+            N.check(lib.igs_l1_ssim_finish(part.data_ptr(), C_, H, W, float(lambda_dssim), out3.data_ptr(), stream),
+                    "l1_ssim finish")
         ctx.save_for_backward(x, y, maps)
         ctx.lam = float(lambda_dssim)
-        loss = sums[1] + ctx.lam * (1.0 - sums[0])
-        return loss, sums[1], sums[0]
+        return out3[0], out3[1], out3[2]
 
     @staticmethod
     def backward(ctx, g_loss, g_l1, g_ssim):

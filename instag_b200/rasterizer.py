@@ -107,9 +107,15 @@ def _ptr(t):
 
 
 def _f32c(t):
+    """fp32, contiguous and 16-byte aligned (the kernels use vector accesses; a contiguous view at an
+    odd storage offset -- which the reference accepts -- is copied)."""
     if t.dtype != torch.float32:
         t = t.float()
-    return t if t.is_contiguous() else t.contiguous()
+    if not t.is_contiguous():
+        return t.contiguous()
+    if t.numel() and t.data_ptr() % 16:
+        return t.clone()
+    return t
 
 
 class GaussianRasterizationSettings(NamedTuple):

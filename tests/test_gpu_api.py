@@ -109,6 +109,38 @@ def test_non_contiguous_and_sentinel_inputs():
         assert torch.equal(a, b)
 
 
+def test_misaligned_views_are_accepted_like_the_reference_does():
+    """A contiguous view at an odd storage offset (data_ptr % 16 != 0): the host sides copy it, the C ABI
+    itself refuses it cleanly (the kernels' 16-byte accesses would fault and poison the context)."""
+    from instag_b200 import _native as N
+    from instag_b200 import rasterizer as R
+    sc = U.make_scene(P=801, W=48, H=48, seed=24)
+    base, _ = _call(sc, requires_grad=False)
+    t = U.to_torch(sc)
+    odd = {}
+    for k in ("means3D", "scales", "rotations", "colors_precomp", "opacities"):
+        flat = torch.zeros(t[k].numel() + 1, device="cuda")
+        flat[1:] = t[k].reshape(-1)
+        odd[k] = flat[1:].view(t[k].shape)
+        assert odd[k].data_ptr() % 16 != 0 and odd[k].is_contiguous()
+    out, _ = _call(sc, requires_grad=False, **odd)
+    for a, b in zip(base, out):
+        assert torch.equal(a, b)
+    # the C ABI with a misaligned pointer: IGS_ERR_INVALID, not a fault
+    R._forward_native(*U.raw_args_fwd(t))
+    torch.cuda.synchronize()
+    dev = t["means3D"].device
+    s = R._get_scratch(dev, torch.cuda.current_stream(dev).cuda_stream)
+    keep = s.fwd_args.means3D
+    s.fwd_args.means3D = odd["means3D"].data_ptr()
+    try:
+        assert N.lib().igs_forward(s.fwd_args_ref, torch.cuda.current_stream(dev).cuda_stream, s.n_out_ref) == N.IGS_ERR_INVALID
+        assert "aligned" in N.last_error()
+    finally:
+        s.fwd_args.means3D = keep
+    torch.cuda.synchronize()
+
+
 def test_mark_visible():
     from diff_gauss import GaussianRasterizer
     sc = U.make_scene(P=4000, W=32, H=32, seed=3, extent=0.8)

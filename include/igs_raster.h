@@ -310,6 +310,22 @@ int igs_l1_ssim_backward(const float* img1, const float* img2, const float* dA, 
                          const float* dC, int32_t C, int32_t H, int32_t W, float lambda_dssim,
                          const float* grad_out, float* grad_img1, igs_stream_t stream);
 
+/* igs_l1_ssim_forward_static: igs_l1_ssim_forward + igs_l1_ssim_finish with no caller scratch.
+ *     NO COUNTERPART IN THE REFERENCE: added for callers that
+ *     cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses that forbid
+ *     cudaMalloc).  The per-CTA partial sums go to a file-scope `static __device__` array inside the
+ *     library (512 KB, held by every GPU that loads the library until exit) instead of a caller
+ *     workspace; the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ *     Limit: igs_l1_ssim_partials(C,H,W) <= 65536, i.e. up to [3,2048,2048]; larger frames are refused
+ *     with IGS_ERR_INVALID (use igs_l1_ssim_forward with a workspace).  The caller passes the inputs and
+ *     the outputs: dA, dB, dC ([C,H,W] each, kept for igs_l1_ssim_backward) and out3 = {loss, Ll1, ssim}.
+ *     Every call on a device shares the one array and finds the last call's contents in it (none of them
+ *     is read: each call overwrites the pairs it then sums); calls that OVERLAP on the GPU -- different
+ *     streams, or host threads, on one device -- race on it and must be serialised by the caller. */
+int igs_l1_ssim_forward_static(const float* img1, const float* img2, int32_t C, int32_t H, int32_t W,
+                               float lambda_dssim, float* dA, float* dB, float* dC, float* out3,
+                               igs_stream_t stream);
+
 /* f3 (the rest)  igs_geom_loss_* replace the geometry regularisers train_face.py computes on the
  *     rasterizer's depth / normal / alpha images (/root/reference/train_face.py:469, :481-491 with
  *     utils/loss_utils.py:17-20 `normalize`, :540):

@@ -90,6 +90,7 @@ SYMBOLS = {
     "igs_l1_ssim_forward": (C.c_int, [_p, _p, C.c_int32, C.c_int32, C.c_int32, _p, _p, _p, _p, _p]),
     "igs_l1_ssim_finish": (C.c_int, [_p, C.c_int32, C.c_int32, C.c_int32, C.c_float, _p, _p]),
     "igs_l1_ssim_backward": (C.c_int, [_p, _p, _p, _p, _p, C.c_int32, C.c_int32, C.c_int32, C.c_float, _p, _p, _p]),
+    "igs_l1_ssim_forward_static": (C.c_int, [_p, _p, C.c_int32, C.c_int32, C.c_int32, C.c_float, _p, _p, _p, _p, _p]),
     "igs_geom_loss_workspace": (C.c_size_t, [C.c_int32]),
     "igs_geom_loss_forward": (C.c_int, [_p] * 8 + [C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_float, _p, _p, _p]),
     "igs_geom_loss_backward": (C.c_int, [_p] * 6 + [C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_float] + [_p] * 6),

@@ -15,6 +15,7 @@
 // HBM bound: forward reads 2 and writes 3 floats per pixel-channel, backward reads 5, writes 1.
 #include "igs_common.cuh"
 #include "igs_kernels.cuh"
+#include <mutex>
 
 namespace igs {
 
@@ -221,3 +222,62 @@ int igs_l1_ssim_backward(const float* img1, const float* img2, const float* dA, 
 }
 
 } // extern "C"
+
+// ---- igs_l1_ssim_forward_static: the forward + finish pair with NO caller scratch --------------
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc): the per-CTA partial sums live in a file-scope device array instead of a caller
+// workspace.  Every GPU that loads the library holds the array (512 KB) until exit.  No counterpart in
+// the reference.
+constexpr size_t STATIC_PARTIALS_MAX = 65536; // {ssim, l1} pairs: up to 3 x 2048 x 2048 (49152 CTAs)
+static __device__ __align__(256) float g_static_partials[2 * STATIC_PARTIALS_MAX];
+
+// In host code g_static_partials is only a stand-in for the symbol, not a device address: the
+// address a kernel can use comes from cudaGetSymbolAddress, once per device, with that device current.
+constexpr int STATIC_MAX_DEVICES = 64;
+static float* static_partials_on_current_device(int* status) {
+  static std::mutex mu;
+  static float* ptr[STATIC_MAX_DEVICES] = {};
+  int dev = -1;
+  *status = check_cuda(cudaGetDevice(&dev), "l1_ssim forward_static: cudaGetDevice");
+  if (*status != IGS_OK) return nullptr;
+  if (dev < 0 || dev >= STATIC_MAX_DEVICES) {
+    set_error("l1_ssim forward_static: device %d beyond the %d devices supported", dev, STATIC_MAX_DEVICES);
+    *status = IGS_ERR_INVALID;
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr[dev]) {
+    float* p = nullptr;
+    *status = check_cuda(cudaGetSymbolAddress((void**)&p, g_static_partials),
+                         "l1_ssim forward_static: cudaGetSymbolAddress");
+    if (*status != IGS_OK) return nullptr;
+    ptr[dev] = p;
+  }
+  return ptr[dev];
+}
+
+extern "C" int igs_l1_ssim_forward_static(const float* img1, const float* img2, int32_t C, int32_t H, int32_t W,
+                                          float lambda_dssim, float* dA, float* dB, float* dC, float* out3,
+                                          igs_stream_t stream) {
+  if (C <= 0 || H <= 0 || W <= 0 || !img1 || !img2 || !dA || !dB || !dC || !out3) {
+    set_error("l1_ssim forward_static: bad arguments"); return IGS_ERR_INVALID;
+  }
+  const size_t n = igs_l1_ssim_partials(C, H, W);
+  if (n > STATIC_PARTIALS_MAX) {
+    set_error("l1_ssim forward_static: %d x %d x %d needs %zu partial sums, the static scratch holds %zu "
+              "(use igs_l1_ssim_forward with a caller workspace)", C, H, W, n, STATIC_PARTIALS_MAX);
+    return IGS_ERR_INVALID;
+  }
+  int status = IGS_OK;
+  float* partial = static_partials_on_current_device(&status);
+  if (!partial) return status;
+  // Nothing in the array has to start at zero: every CTA of the forward kernel overwrites its own pair
+  // and the finish kernel reads exactly the n pairs of this call, so what the last call left is dead.
+  static const Win win = make_window();
+  const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C);
+  l1_ssim_forward_kernel<<<grid, LT * LT, 0, (cudaStream_t)stream>>>(img1, img2, H, W, win, dA, dB, dC, partial);
+  l1_ssim_finish_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(partial, (int)n, 1.0f / ((float)C * (float)H * (float)W),
+                                                            lambda_dssim, out3);
+  count_launch(2);
+  return stage_check(false, (cudaStream_t)stream, "l1_ssim forward_static");
+}

@@ -316,7 +316,7 @@ int igs_l1_ssim_backward(const float* img1, const float* img2, const float* dA, 
  *     cudaMalloc).  The per-CTA partial sums go to a file-scope `static __device__` array inside the
  *     library (512 KB, held by every GPU that loads the library until exit) instead of a caller
  *     workspace; the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
- *     Limit: igs_l1_ssim_partials(C,H,W) <= 65536, i.e. up to [3,2048,2048]; larger frames are refused
+ *     Limit: igs_l1_ssim_partials(C,H,W) <= 65536, i.e. up to [3,4096,4096]; larger frames are refused
  *     with IGS_ERR_INVALID (use igs_l1_ssim_forward with a workspace).  The caller passes the inputs and
  *     the outputs: dA, dB, dC ([C,H,W] each, kept for igs_l1_ssim_backward) and out3 = {loss, Ll1, ssim}.
  *     Every call on a device shares the one array and finds the last call's contents in it (none of them

@@ -4,7 +4,7 @@
 // dL/dimage -- the rasterizer backward's dL_dcolor input -- directly in CHW layout:
 //
 //   forward : per channel, separable 11-tap Gaussian window (sigma 1.5, zero padding 5) of
-//             {x, y, x^2, y^2, xy} through shared memory -> SSIM map -> per-CTA partial sums of
+//             {x, y, x^2, y^2, xy} through shared memory, 4 outputs per thread along the window -> SSIM map -> per-CTA partial sums of
 //             the SSIM map and of |x - y|, plus three per-pixel derivative maps
 //                 A = df/dmu1 - 2 mu1 df/ds1 - mu2 df/ds12,  B = df/ds1,  C = df/ds12
 //   backward: dL/dx = g * ( sign(x - y)/N - lambda/N * (conv(A) + 2 x conv(B) + y conv(C)) )
@@ -19,9 +19,10 @@
 
 namespace igs {
 
-constexpr int LT = 16;            // output tile edge
+constexpr int QT = 32;            // output tile edge
 constexpr int LH = 5;             // window radius (window_size 11)
-constexpr int LR = LT + 2 * LH;   // 26 rows / columns with halo
+constexpr int QR = QT + 2 * LH;   // 42 rows / columns with halo
+constexpr int QTHREADS = 256;     // 8 warps: a warp owns 4 output rows, a lane one column
 constexpr float SSIM_C1 = 0.01f * 0.01f, SSIM_C2 = 0.03f * 0.03f;
 
 struct Win { float w[11]; };
@@ -35,64 +36,100 @@ static Win make_window() {
   return k;
 }
 
-__global__ void __launch_bounds__(LT * LT) l1_ssim_forward_kernel(
+// Four neighbouring outputs of the 11-tap window from the 14 inputs they share, all in registers:
+// 14 shared-memory loads per 4 outputs instead of 44.  Taps in ascending order from 0, as a thread
+// that owned one output would add them.
+__device__ __forceinline__ void taps4(const Win& win, const float (&in)[14], float (&out)[4]) {
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 11; k++) s = fmaf(win.w[k], in[j + k], s);
+    out[j] = s;
+  }
+}
+
+__global__ void __launch_bounds__(QTHREADS) l1_ssim_forward_kernel(
     const float* __restrict__ img1, const float* __restrict__ img2, int H, int W, Win win,
     float* __restrict__ dA, float* __restrict__ dB, float* __restrict__ dC, float* __restrict__ partial) {
-  __shared__ float s_x[LR][LR + 1], s_y[LR][LR + 1];
-  __shared__ float s_h[5][LR][LT + 1];
-  __shared__ float s_red[2][LT * LT / 32];
-  const int c = blockIdx.z, tx = threadIdx.x % LT, ty = threadIdx.x / LT;
-  const int x0 = blockIdx.x * LT, y0 = blockIdx.y * LT;
+  __shared__ float s_x[QR][QR + 1], s_y[QR][QR + 1];
+  __shared__ float s_h[5][QR][QT + 1];
+  __shared__ float s_red[2][QTHREADS / 32];
+  const int c = blockIdx.z;
+  const int x0 = blockIdx.x * QT, y0 = blockIdx.y * QT;
   const size_t plane = (size_t)c * H * W;
-  for (int i = threadIdx.x; i < LR * LR; i += LT * LT) {
-    const int ry = i / LR, rx = i % LR, gx = x0 - LH + rx, gy = y0 - LH + ry;
+  for (int i = threadIdx.x; i < QR * QR; i += QTHREADS) {
+    const int ry = i / QR, rx = i - ry * QR, gx = x0 - LH + rx, gy = y0 - LH + ry;
     const bool in = gx >= 0 && gx < W && gy >= 0 && gy < H;
     s_x[ry][rx] = in ? __ldg(img1 + plane + (size_t)gy * W + gx) : 0.f;
     s_y[ry][rx] = in ? __ldg(img2 + plane + (size_t)gy * W + gx) : 0.f;
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < LR * LT; i += LT * LT) { // horizontal pass, 26 rows x 16 columns
-    const int ry = i / LT, rx = i % LT;
-    float sx = 0.f, sy = 0.f, sxx = 0.f, syy = 0.f, sxy = 0.f;
+  // horizontal pass: 42 rows x 8 groups of 4 columns; a group reads its 14 x and 14 y once
+  for (int it = threadIdx.x; it < QR * (QT / 4); it += QTHREADS) {
+    const int ry = it >> 3, cg = (it & 7) * 4;
+    float a[14], b[14], t[14], o[4];
 #pragma unroll
-    for (int k = 0; k < 11; k++) {
-      const float w = win.w[k], a = s_x[ry][rx + k], b = s_y[ry][rx + k];
-      sx = fmaf(w, a, sx); sy = fmaf(w, b, sy);
-      sxx = fmaf(w, a * a, sxx); syy = fmaf(w, b * b, syy); sxy = fmaf(w, a * b, sxy);
-    }
-    s_h[0][ry][rx] = sx; s_h[1][ry][rx] = sy; s_h[2][ry][rx] = sxx; s_h[3][ry][rx] = syy; s_h[4][ry][rx] = sxy;
+    for (int k = 0; k < 14; k++) { a[k] = s_x[ry][cg + k]; b[k] = s_y[ry][cg + k]; }
+    taps4(win, a, o);
+#pragma unroll
+    for (int j = 0; j < 4; j++) s_h[0][ry][cg + j] = o[j];
+    taps4(win, b, o);
+#pragma unroll
+    for (int j = 0; j < 4; j++) s_h[1][ry][cg + j] = o[j];
+#pragma unroll
+    for (int k = 0; k < 14; k++) t[k] = a[k] * a[k];
+    taps4(win, t, o);
+#pragma unroll
+    for (int j = 0; j < 4; j++) s_h[2][ry][cg + j] = o[j];
+#pragma unroll
+    for (int k = 0; k < 14; k++) t[k] = b[k] * b[k];
+    taps4(win, t, o);
+#pragma unroll
+    for (int j = 0; j < 4; j++) s_h[3][ry][cg + j] = o[j];
+#pragma unroll
+    for (int k = 0; k < 14; k++) t[k] = a[k] * b[k];
+    taps4(win, t, o);
+#pragma unroll
+    for (int j = 0; j < 4; j++) s_h[4][ry][cg + j] = o[j];
   }
   __syncthreads();
-  float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+  // vertical pass: lane = column, 4 rows per thread from the 14 rows they share
+  const int tx = threadIdx.x & 31, r0 = (threadIdx.x >> 5) * 4;
+  float v[5][4];
 #pragma unroll
-  for (int k = 0; k < 11; k++) { // vertical pass
-    const float w = win.w[k];
-    mu1 = fmaf(w, s_h[0][ty + k][tx], mu1); mu2 = fmaf(w, s_h[1][ty + k][tx], mu2);
-    e11 = fmaf(w, s_h[2][ty + k][tx], e11); e22 = fmaf(w, s_h[3][ty + k][tx], e22);
-    e12 = fmaf(w, s_h[4][ty + k][tx], e12);
+  for (int m = 0; m < 5; m++) {
+    float in[14];
+#pragma unroll
+    for (int k = 0; k < 14; k++) in[k] = s_h[m][r0 + k][tx];
+    taps4(win, in, v[m]);
   }
-  const int x = x0 + tx, y = y0 + ty;
-  const bool inside = x < W && y < H;
+  const int x = x0 + tx;
   float ssim_v = 0.f, l1_v = 0.f;
-  if (inside) {
-    // utils/loss_utils.py:58-70
-    const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
-    const float s1 = e11 - mu1_sq, s2 = e22 - mu2_sq, s12 = e12 - mu12;
-    const float a1 = 2.f * mu12 + SSIM_C1, a2 = 2.f * s12 + SSIM_C2;
-    const float b1 = mu1_sq + mu2_sq + SSIM_C1, b2 = s1 + s2 + SSIM_C2;
-    const float inv = 1.f / (b1 * b2);
-    const float f = a1 * a2 * inv;
-    ssim_v = f;
-    const float df_dmu1 = 2.f * mu2 * a2 * inv - f * 2.f * mu1 / b1;
-    const float df_ds1 = -f / b2;
-    const float df_ds12 = 2.f * a1 * inv;
-    const size_t pix = plane + (size_t)y * W + x;
-    dA[pix] = df_dmu1 - 2.f * mu1 * df_ds1 - mu2 * df_ds12;
-    dB[pix] = df_ds1;
-    dC[pix] = df_ds12;
-    l1_v = fabsf(s_x[ty + LH][tx + LH] - s_y[ty + LH][tx + LH]);
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    const int y = y0 + r0 + j;
+    if (x < W && y < H) {
+      // utils/loss_utils.py:58-70
+      const float mu1 = v[0][j], mu2 = v[1][j], e11 = v[2][j], e22 = v[3][j], e12 = v[4][j];
+      const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
+      const float s1 = e11 - mu1_sq, s2 = e22 - mu2_sq, s12 = e12 - mu12;
+      const float a1 = 2.f * mu12 + SSIM_C1, a2 = 2.f * s12 + SSIM_C2;
+      const float b1 = mu1_sq + mu2_sq + SSIM_C1, b2 = s1 + s2 + SSIM_C2;
+      const float inv = 1.f / (b1 * b2);
+      const float f = a1 * a2 * inv;
+      ssim_v += f;
+      const float df_dmu1 = 2.f * mu2 * a2 * inv - f * 2.f * mu1 / b1;
+      const float df_ds1 = -f / b2;
+      const float df_ds12 = 2.f * a1 * inv;
+      const size_t pix = plane + (size_t)y * W + x;
+      dA[pix] = df_dmu1 - 2.f * mu1 * df_ds1 - mu2 * df_ds12;
+      dB[pix] = df_ds1;
+      dC[pix] = df_ds12;
+      l1_v += fabsf(s_x[r0 + j + LH][tx + LH] - s_y[r0 + j + LH][tx + LH]);
+    }
   }
-  // per-CTA partial sums (summed by the host wrapper: deterministic, no float atomics)
+  // per-CTA partial sums (summed by the finish kernel in a fixed order: deterministic, no float atomics)
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     ssim_v += __shfl_xor_sync(0xffffffffu, ssim_v, o);
@@ -103,24 +140,24 @@ __global__ void __launch_bounds__(LT * LT) l1_ssim_forward_kernel(
   __syncthreads();
   if (threadIdx.x == 0) {
     float a = 0.f, b = 0.f;
-    for (int w = 0; w < LT * LT / 32; w++) { a += s_red[0][w]; b += s_red[1][w]; }
+    for (int w = 0; w < QTHREADS / 32; w++) { a += s_red[0][w]; b += s_red[1][w]; }
     const size_t cta = ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
     partial[2 * cta] = a;
     partial[2 * cta + 1] = b;
   }
 }
 
-__global__ void __launch_bounds__(LT * LT) l1_ssim_backward_kernel(
+__global__ void __launch_bounds__(QTHREADS) l1_ssim_backward_kernel(
     const float* __restrict__ img1, const float* __restrict__ img2, const float* __restrict__ dA,
     const float* __restrict__ dB, const float* __restrict__ dC, int H, int W, Win win, float lambda_dssim,
     const float* __restrict__ grad_out, float inv_n, float* __restrict__ grad_img1) {
-  __shared__ float s_m[3][LR][LR + 1];
-  __shared__ float s_h[3][LR][LT + 1];
-  const int c = blockIdx.z, tx = threadIdx.x % LT, ty = threadIdx.x / LT;
-  const int x0 = blockIdx.x * LT, y0 = blockIdx.y * LT;
+  __shared__ float s_m[3][QR][QR + 1];
+  __shared__ float s_h[3][QR][QT + 1];
+  const int c = blockIdx.z;
+  const int x0 = blockIdx.x * QT, y0 = blockIdx.y * QT;
   const size_t plane = (size_t)c * H * W;
-  for (int i = threadIdx.x; i < LR * LR; i += LT * LT) {
-    const int ry = i / LR, rx = i % LR, gx = x0 - LH + rx, gy = y0 - LH + ry;
+  for (int i = threadIdx.x; i < QR * QR; i += QTHREADS) {
+    const int ry = i / QR, rx = i - ry * QR, gx = x0 - LH + rx, gy = y0 - LH + ry;
     const bool in = gx >= 0 && gx < W && gy >= 0 && gy < H;
     const size_t p = plane + (size_t)gy * W + gx;
     s_m[0][ry][rx] = in ? __ldg(dA + p) : 0.f;
@@ -128,31 +165,42 @@ __global__ void __launch_bounds__(LT * LT) l1_ssim_backward_kernel(
     s_m[2][ry][rx] = in ? __ldg(dC + p) : 0.f;
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < LR * LT; i += LT * LT) {
-    const int ry = i / LT, rx = i % LT;
-    float a = 0.f, b = 0.f, d = 0.f;
+  for (int it = threadIdx.x; it < QR * (QT / 4); it += QTHREADS) {
+    const int ry = it >> 3, cg = (it & 7) * 4;
 #pragma unroll
-    for (int k = 0; k < 11; k++) {
-      const float w = win.w[k];
-      a = fmaf(w, s_m[0][ry][rx + k], a); b = fmaf(w, s_m[1][ry][rx + k], b); d = fmaf(w, s_m[2][ry][rx + k], d);
+    for (int m = 0; m < 3; m++) {
+      float in[14], o[4];
+#pragma unroll
+      for (int k = 0; k < 14; k++) in[k] = s_m[m][ry][cg + k];
+      taps4(win, in, o);
+#pragma unroll
+      for (int j = 0; j < 4; j++) s_h[m][ry][cg + j] = o[j];
     }
-    s_h[0][ry][rx] = a; s_h[1][ry][rx] = b; s_h[2][ry][rx] = d;
   }
   __syncthreads();
-  const int x = x0 + tx, y = y0 + ty;
-  if (x >= W || y >= H) return;
-  float ca = 0.f, cb = 0.f, cc = 0.f;
+  const int tx = threadIdx.x & 31, r0 = (threadIdx.x >> 5) * 4;
+  float v[3][4];
 #pragma unroll
-  for (int k = 0; k < 11; k++) {
-    const float w = win.w[k];
-    ca = fmaf(w, s_h[0][ty + k][tx], ca); cb = fmaf(w, s_h[1][ty + k][tx], cb); cc = fmaf(w, s_h[2][ty + k][tx], cc);
+  for (int m = 0; m < 3; m++) {
+    float in[14];
+#pragma unroll
+    for (int k = 0; k < 14; k++) in[k] = s_h[m][r0 + k][tx];
+    taps4(win, in, v[m]);
   }
-  const size_t pix = plane + (size_t)y * W + x;
-  const float xv = __ldg(img1 + pix), yv = __ldg(img2 + pix);
-  const float d = xv - yv;
-  const float sgn = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f); // torch.abs backward: sign(0) = 0
-  const float dssim = ca + 2.f * xv * cb + yv * cc;          // sum_q d ssim_q / d x_p
-  grad_img1[pix] = __ldg(grad_out) * inv_n * (sgn - lambda_dssim * dssim);
+  const int x = x0 + tx;
+  if (x >= W) return;
+  const float g = __ldg(grad_out) * inv_n;
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    const int y = y0 + r0 + j;
+    if (y >= H) break;
+    const size_t pix = plane + (size_t)y * W + x;
+    const float xv = __ldg(img1 + pix), yv = __ldg(img2 + pix);
+    const float d = xv - yv;
+    const float sgn = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f); // torch.abs backward: sign(0) = 0
+    const float dssim = v[0][j] + 2.f * xv * v[1][j] + yv * v[2][j]; // sum_q d ssim_q / d x_p
+    grad_img1[pix] = g * (sgn - lambda_dssim * dssim);
+  }
 }
 
 // {loss, Ll1, ssim} from the forward kernel's per-CTA partial sums, in a fixed order (deterministic)
@@ -191,7 +239,7 @@ int igs_l1_ssim_finish(const float* partial, int32_t C, int32_t H, int32_t W, fl
 }
 
 size_t igs_l1_ssim_partials(int32_t C, int32_t H, int32_t W) {
-  return (size_t)(C > 0 ? C : 0) * ((H + LT - 1) / LT) * ((W + LT - 1) / LT);
+  return (size_t)(C > 0 ? C : 0) * ((H + QT - 1) / QT) * ((W + QT - 1) / QT);
 }
 
 int igs_l1_ssim_forward(const float* img1, const float* img2, int32_t C, int32_t H, int32_t W, float* dA,
@@ -200,8 +248,8 @@ int igs_l1_ssim_forward(const float* img1, const float* img2, int32_t C, int32_t
     set_error("l1_ssim forward: bad arguments"); return IGS_ERR_INVALID;
   }
   static const Win win = make_window();
-  const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C);
-  l1_ssim_forward_kernel<<<grid, LT * LT, 0, (cudaStream_t)stream>>>(img1, img2, H, W, win, dA, dB, dC, partial);
+  const dim3 grid((W + QT - 1) / QT, (H + QT - 1) / QT, C);
+  l1_ssim_forward_kernel<<<grid, QTHREADS, 0, (cudaStream_t)stream>>>(img1, img2, H, W, win, dA, dB, dC, partial);
   count_launch();
   return stage_check(false, (cudaStream_t)stream, "l1_ssim forward");
 }
@@ -213,9 +261,9 @@ int igs_l1_ssim_backward(const float* img1, const float* img2, const float* dA, 
     set_error("l1_ssim backward: bad arguments"); return IGS_ERR_INVALID;
   }
   static const Win win = make_window();
-  const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C);
+  const dim3 grid((W + QT - 1) / QT, (H + QT - 1) / QT, C);
   const float inv_n = 1.0f / ((float)C * (float)H * (float)W);
-  l1_ssim_backward_kernel<<<grid, LT * LT, 0, (cudaStream_t)stream>>>(img1, img2, dA, dB, dC, H, W, win, lambda_dssim,
+  l1_ssim_backward_kernel<<<grid, QTHREADS, 0, (cudaStream_t)stream>>>(img1, img2, dA, dB, dC, H, W, win, lambda_dssim,
                                                                       grad_out, inv_n, grad_img1);
   count_launch();
   return stage_check(false, (cudaStream_t)stream, "l1_ssim backward");
@@ -228,7 +276,7 @@ int igs_l1_ssim_backward(const float* img1, const float* img2, const float* dA, 
 // cudaMalloc): the per-CTA partial sums live in a file-scope device array instead of a caller
 // workspace.  Every GPU that loads the library holds the array (512 KB) until exit.  No counterpart in
 // the reference.
-constexpr size_t STATIC_PARTIALS_MAX = 65536; // {ssim, l1} pairs: up to 3 x 2048 x 2048 (49152 CTAs)
+constexpr size_t STATIC_PARTIALS_MAX = 65536; // {ssim, l1} pairs: up to 3 x 4096 x 4096 (49152 CTAs)
 static __device__ __align__(256) float g_static_partials[2 * STATIC_PARTIALS_MAX];
 
 // In host code g_static_partials is only a stand-in for the symbol, not a device address: the
@@ -274,8 +322,8 @@ extern "C" int igs_l1_ssim_forward_static(const float* img1, const float* img2, 
   // Nothing in the array has to start at zero: every CTA of the forward kernel overwrites its own pair
   // and the finish kernel reads exactly the n pairs of this call, so what the last call left is dead.
   static const Win win = make_window();
-  const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C);
-  l1_ssim_forward_kernel<<<grid, LT * LT, 0, (cudaStream_t)stream>>>(img1, img2, H, W, win, dA, dB, dC, partial);
+  const dim3 grid((W + QT - 1) / QT, (H + QT - 1) / QT, C);
+  l1_ssim_forward_kernel<<<grid, QTHREADS, 0, (cudaStream_t)stream>>>(img1, img2, H, W, win, dA, dB, dC, partial);
   l1_ssim_finish_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(partial, (int)n, 1.0f / ((float)C * (float)H * (float)W),
                                                             lambda_dssim, out3);
   count_launch(2);

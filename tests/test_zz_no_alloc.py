@@ -73,10 +73,10 @@ def test_static_scratch_forward_refuses_frames_beyond_its_array():
     import torch
     from instag_b200 import _native as N
     lib = N.lib()
-    assert lib.igs_l1_ssim_partials(3, 2048, 2048) <= 65536 < lib.igs_l1_ssim_partials(3, 2400, 2400)
+    assert lib.igs_l1_ssim_partials(3, 4096, 4096) <= 65536 < lib.igs_l1_ssim_partials(3, 4800, 4800)
     t = torch.zeros((16,), dtype=torch.float32, device="cuda")   # never dereferenced: refused before any launch
     p = t.data_ptr()
-    rc = lib.igs_l1_ssim_forward_static(p, p, 3, 2400, 2400, LAMBDA, p, p, p, p, torch.cuda.current_stream().cuda_stream)
+    rc = lib.igs_l1_ssim_forward_static(p, p, 3, 4800, 4800, LAMBDA, p, p, p, p, torch.cuda.current_stream().cuda_stream)
     assert rc != 0
     msg = lib.igs_last_error().decode()
     assert "static scratch" in msg and "65536" in msg, msg

@@ -24,6 +24,7 @@
 // Bound: FP32 issue.  Per evaluated pair ~15 flop + 1 MUFU.EX2, per blended
 // pair +17 flop.  DRAM floor: 64 B per instance + 40 B per pixel.
 #include <cstdlib>
+#include <type_traits>
 #include "igs_common.cuh"
 #include "igs_kernels.cuh"
 
@@ -44,6 +45,9 @@ __device__ __forceinline__ uint32_t smid() {
 constexpr int RW = 4;           // warps per CTA: one per SM sub-partition
 constexpr int RT = RW * 32;     // threads per CTA
 constexpr int RG = 4;           // survivors composited per trip of the inner loop
+#ifndef IGS_FWD_MIN_CTAS
+#define IGS_FWD_MIN_CTAS 5       // resident CTAs per SM the register budget is cut for (launch_render caps at 5)
+#endif
 
 __device__ __forceinline__ float4 lds128(uint32_t addr) {
   float4 v;
@@ -65,7 +69,7 @@ __device__ __forceinline__ void copies_wait() { asm volatile("cp.async.wait_grou
 // 8x4 block) units from one global ticket, heaviest tiles first (tile_order), until the
 // frame is done -- the four sub-partitions of an SM stay evenly loaded to the end.
 template <int ED_T> // 0, 1, or -1 = generic (runtime ED up to IGS_MAX_EXTRA_DIMS)
-__global__ void __launch_bounds__(RT, 6) render_kernel(RenderArgs a) {
+__global__ void __launch_bounds__(RT, IGS_FWD_MIN_CTAS) render_kernel(RenderArgs a) {
   // per warp, 3 KB: planes r0, r1 of the chunk's survivors (stored by the survivors after the cull,
   // from the registers the cull data was prefetched into), and, double buffered, planes r2, r3 of
   // EVERY entry of the chunk, copied in asynchronously one chunk ahead (cp.async: no register in
@@ -171,50 +175,69 @@ __global__ void __launch_bounds__(RT, 6) render_kernel(RenderArgs a) {
       if (ED_T < 0) s_id[warp][lane] = id_mine;
     }
     __syncwarp();
-    while (m) {
-      // FOUR survivors per trip.  Their alpha chains are independent (instruction-level
-      // parallelism for a warp that is alone on its scheduler at the end of the frame); only the
-      // transmittance recurrence is ordered, and it is written branch-free: a splat that does
-      // not blend gets weight 0 and leaves T alone.
-      int j[RG];
-      bool have[RG];
+    // G survivors per trip.  Their alpha chains are independent (instruction-level parallelism for a
+    // warp that is alone on its scheduler at the end of the frame); only the transmittance recurrence is
+    // ordered.  A trip first runs it WITHOUT the stop test -- a splat that does not blend gets alpha 0,
+    // which leaves T alone (T * (1 - 0) = T exactly) and weighs nothing: T only ever shrinks, so if it is
+    // still >= T_MIN after the trip no pixel stopped inside it, and the products are the reference's, in
+    // its order.  Only the trips in which a pixel does stop (at most once per pixel and unit) repeat
+    // the recurrence with the reference's test after every splat.
+    auto trip = [&](auto width) {
+      constexpr int G = decltype(width)::value;
+      int j[G];
+      bool have[G];
 #pragma unroll
-      for (int h = 0; h < RG; h++) {
+      for (int h = 0; h < G; h++) {
         have[h] = m != 0;
         j[h] = have[h] ? __ffs(m) - 1 : j[h ? h - 1 : 0];
         m &= m - 1;
       }
-      float alpha[RG], zd[RG], ze[RG];
-      bool ok[RG];
+      float alpha[G], zd[G], ze[G];
+      bool ok[G];
 #pragma unroll
-      for (int h = 0; h < RG; h++) {
+      for (int h = 0; h < G; h++) {
         const float4 r1 = lds128(sbase + 512 + j[h] * 16), r0 = lds128(sbase + j[h] * 16);
         const float dx = __fsub_rn(r1.x, pxf), dy = __fsub_rn(r1.y, pyf);
         const float pw = gauss_power(r0.x, r0.y, r0.z, dx, dy);
         alpha[h] = fminf(0.99f, __fmul_rn(r0.w, expf(pw)));
-        ok[h] = have[h] && !(pw > 0.0f) && !(alpha[h] < ALPHA_MIN);
+        ok[h] = have[h] && !done && !(pw > 0.0f) && !(alpha[h] < ALPHA_MIN);
         zd[h] = r1.z; ze[h] = r1.w;
       }
-      // ordered part: T, done, last contributor (bit-exact with the reference), blend weights
-      float w[RG];
+      float w[G];
+      float Tn = T;
       bool any = false;
 #pragma unroll
-      for (int h = 0; h < RG; h++) {
-        const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha[h]));
-        const bool live_h = ok[h] && !done;
-        const bool stop = test_T < T_MIN;
-        const bool blend = live_h && !stop;
-        done = done || (live_h && stop);
-        w[h] = blend ? __fmul_rn(alpha[h], T) : 0.f;
-        T = blend ? test_T : T;
-        last_contributor = blend ? (uint32_t)(cb + j[h] + 1) : last_contributor;
-        any = any || blend;
+      for (int h = 0; h < G; h++) {
+        const float am = ok[h] ? alpha[h] : 0.f;
+        w[h] = __fmul_rn(am, Tn);
+        Tn = __fmul_rn(Tn, __fsub_rn(1.f, am));
+        any = any || ok[h];
       }
-      if (!__any_sync(0xffffffffu, any)) continue;
+      if (!__any_sync(0xffffffffu, Tn < T_MIN)) {
+        T = Tn;
+#pragma unroll
+        for (int h = 0; h < G; h++) last_contributor = ok[h] ? (uint32_t)(cb + j[h] + 1) : last_contributor;
+      } else {
+        // ordered part with the stop test: T, done, last contributor (bit-exact with the reference)
+        any = false;
+#pragma unroll
+        for (int h = 0; h < G; h++) {
+          const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha[h]));
+          const bool live_h = ok[h] && !done;
+          const bool stop = test_T < T_MIN;
+          const bool blend = live_h && !stop;
+          done = done || (live_h && stop);
+          w[h] = blend ? __fmul_rn(alpha[h], T) : 0.f;
+          T = blend ? test_T : T;
+          last_contributor = blend ? (uint32_t)(cb + j[h] + 1) : last_contributor;
+          any = any || blend;
+        }
+      }
+      if (!__any_sync(0xffffffffu, any)) return;
       // X += f*(alpha*T): one rounding away from the reference's fma(f*alpha, T, X)
       // (forward.cu:425-431), far inside the 1e-5 image tolerance
 #pragma unroll
-      for (int h = 0; h < RG; h++) {
+      for (int h = 0; h < G; h++) {
         const float4 r2 = lds128(cur + j[h] * 16);
         const float4 r3 = lds128(cur + 512 + j[h] * 16);
         C0 = __fmaf_rn(r2.x, w[h], C0);
@@ -232,6 +255,11 @@ __global__ void __launch_bounds__(RT, 6) render_kernel(RenderArgs a) {
           }
         }
       }
+    };
+    // four at a time; a remainder of one or two in a trip half as wide
+    while (m) {
+      if (__popc(m) > RG / 2) trip(std::integral_constant<int, RG>{});
+      else trip(std::integral_constant<int, RG / 2>{});
     }
   }
 

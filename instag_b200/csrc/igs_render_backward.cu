@@ -49,6 +49,9 @@ __device__ __forceinline__ void red_add_v2(float* addr, float x, float y) {
 
 constexpr int PEND = 16;     // parked splats per matrix product (the M of m16n8k8)
 
+#ifndef IGS_BWD_MIN_CTAS
+#define IGS_BWD_MIN_CTAS 6
+#endif
 constexpr int BW = 4;        // warps per CTA: one per SM sub-partition
 constexpr int BT = BW * 32;
 
@@ -60,6 +63,12 @@ __device__ __forceinline__ float4 lds128b(uint32_t addr) {
 __device__ __forceinline__ void sts128b(uint32_t addr, float4 v) {
   asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
+// 4 bytes global -> shared with no register in between (LDGSTS): the list ids two chunks ahead
+__device__ __forceinline__ void copy4_async(uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void copies_commit_b() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void copies_wait_b() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ float rcp_approx(float x) {
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
@@ -76,9 +85,13 @@ struct PixelBack {
 };
 
 template <int ED_T> // 0, 1, or -1 = generic
-__global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a) {
+__global__ void __launch_bounds__(BT, IGS_BWD_MIN_CTAS) render_backward_kernel(BwdRenderArgs a) {
   __shared__ float4 s_rec[BW][4][32];
   __shared__ uint32_t s_id[BW][32];
+  // ids of the chunk after next, copied in asynchronously (double buffered).  In a register the prefetched
+  // id was spilled to local memory at 80 registers, and the spill store waited for the load it had just
+  // issued: 5 % of the kernel's stall samples sat on that one instruction.
+  __shared__ uint32_t s_idn[BW][2][32];
   // parked blend weights [0] and g = G*dL/dalpha [1] of up to PEND splats; pixel p of slot s sits
   // in column p ^ ((s & 1) << 4) so that both the scalar stores and the 16-byte fragment loads are
   // bank-conflict free
@@ -101,6 +114,7 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
   const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(&s_rec[warp][0][0]);
   const uint32_t smine = sbase + lane * 16;
   const uint32_t sidb = (uint32_t)__cvta_generic_to_shared(&s_id[warp][0]);
+  const uint32_t sidn = (uint32_t)__cvta_generic_to_shared(&s_idn[warp][0][lane]); // + 128: the other buffer
   const float bg0 = __ldg(a.bg), bg1 = __ldg(a.bg + 1), bg2 = __ldg(a.bg + 2);
   // mma fragment coordinates: this lane owns rows fg, fg+8 (splat slots) of A and C, and the
   // k-columns ft, ft+4; k-step 2q+h of the product covers pixels 16q + 4*ft + {2h, 2h+1}
@@ -310,10 +324,12 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
 
   // entry e of the reverse walk is list position wmax-1-e (= its `contributor` index)
   const uint32_t* __restrict__ list = a.point_list + range.x;
-  uint32_t id_cur = 0, id_nxt = 0;
+  uint32_t id_cur = 0;
+  uint32_t nbuf = sidn; // where the ids of the NEXT chunk land
   float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f), q1 = q0;
   if (lane < wmax) id_cur = __ldg(list + (wmax - 1 - lane));
-  if (32 + lane < wmax) id_nxt = __ldg(list + (wmax - 33 - lane));
+  if (32 + lane < wmax) copy4_async(nbuf, list + (wmax - 33 - lane));
+  copies_commit_b();
   if (lane < wmax) {
     q0 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4);
     q1 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4 + 1);
@@ -326,12 +342,15 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
     unsigned m = __ballot_sync(0xffffffffu, hit);
     const uint32_t id_mine = id_cur;
     const float4 c0 = q0, c1 = q1;
-    id_cur = id_nxt;
+    copies_wait_b(); // the next chunk's ids (issued one chunk ago; a lane reads the word it copied itself)
     if (cb + 32 + lane < wmax) {
+      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(id_cur) : "r"(nbuf));
       q0 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4);
       q1 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4 + 1);
     }
-    if (cb + 64 + lane < wmax) id_nxt = __ldg(list + (wmax - 65 - cb - lane));
+    nbuf ^= 128u;
+    if (cb + 64 + lane < wmax) copy4_async(nbuf, list + (wmax - 65 - cb - lane));
+    copies_commit_b();
     if (m == 0) continue;
     __syncwarp();
     if (hit) {
@@ -372,6 +391,7 @@ __global__ void __launch_bounds__(BT, 6) render_backward_kernel(BwdRenderArgs a)
     }
   }
   if (pend_at & 511u) flush((int)(pend_at & 511u) >> 4);
+  copies_wait_b();
   __syncwarp(); // the next unit reuses this warp's shared-memory slots
  } // unit loop
   if (lane == 0) stamp_done(a.prof, ST_RBWD);

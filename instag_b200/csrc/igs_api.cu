@@ -377,6 +377,7 @@ int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
   ra.splat = (const float4*)(g + gl.splat);
   ra.extra_attrs = a->extra_attrs; ra.bg = a->bg; ra.out_alpha = a->out_alpha;
   ra.n_contrib = (const uint32_t*)(im + il.n_contrib);
+  ra.info = (const uint32_t*)(im + il.info);
   ra.norm_len = (const float*)(im + il.norm_len);
   ra.normalize = a->normalize_norm != 0;
   ra.out_norm = a->out_norm;

@@ -78,6 +78,7 @@ struct BwdRenderArgs {
   const float* bg;
   const float* out_alpha;
   const uint32_t* n_contrib;
+  const uint32_t* info;   // the frame's {num_rendered, overflowed}: lists and n_contrib of an overflowed frame are not there
   const float *dL_dcolor, *dL_ddepth, *dL_dnorm, *dL_dalpha, *dL_dextra;
   const float* out_norm;  // unit normals of the forward, read when normalize != 0
   const float* norm_len;  // [H*W]

@@ -108,6 +108,12 @@ __global__ void __launch_bounds__(BT, IGS_BWD_MIN_CTAS) render_backward_kernel(B
   if (a.prof.early) pdl_launch_dependents();
   pdl_wait(); // whatever ran before on the stream (the forward, the caller's loss kernels) is complete
   if (threadIdx.x == 0) stamp_begun(a.prof, ST_BWD_START);
+  // a frame that outgrew its instance workspaces was not rendered (a caller that launches the backward
+  // without having read the count -- recorded steps, run-ahead loops -- finds out afterwards)
+  if (__ldg(a.info + 1)) {
+    if (lane == 0) stamp_done(a.prof, ST_RBWD);
+    return;
+  }
   const int num_units = a.grid_x * a.grid_y * 8;
   const int ED = ED_T < 0 ? a.ED : ED_T;
   const size_t HW = (size_t)a.H * a.W;

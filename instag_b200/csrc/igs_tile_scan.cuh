@@ -62,6 +62,7 @@ __device__ __forceinline__ void tile_ranges(const TileScanArgs& a, const bool se
     a.header->overflow = (int64_t)total > a.capacity ? 1u : 0u;
     a.header->render_ticket = 0u;
     a.info[0] = total;
+    a.info[1] = (int64_t)total > a.capacity ? 1u : 0u; // a backward launched without the host having seen the count stands down
     // straight into the caller's pinned host slot: a 4-byte copy-engine transfer between two kernels
     // costs ~12 us of stream time on B200, a posted store costs nothing (the host polls this slot, or
     // reads it when it next needs the count)

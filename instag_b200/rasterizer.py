@@ -23,6 +23,9 @@ def cpu_deep_copy_tuple(input_tuple):
     return tuple(item.cpu().clone() if isinstance(item, torch.Tensor) else item for item in input_tuple)
 
 
+_DEFER_SLOTS = 8  # frames a run-ahead caller may leave unchecked
+
+
 class _DeviceScratch:
     """Reusable scratch of one (device, stream, host thread): the unsorted instance words, the
     control block (tile counters and cursors), the gradient accumulators, the pinned num_rendered
@@ -33,8 +36,12 @@ class _DeviceScratch:
         self.sort = None
         self.ctrl = None
         self.accum = None
-        self.pinned = torch.zeros(4, dtype=torch.int32).pin_memory()
+        # word 0: the count of a call that waits; words 4..: a ring for calls that do not (defer=True)
+        self.pinned = torch.zeros(4 + _DEFER_SLOTS, dtype=torch.int32).pin_memory()
         self.pinned_ptr = self.pinned.data_ptr()
+        self.defer_serial = 0
+        self.defer_pending = []   # (serial, slot, capacity, hint_key), oldest first
+        self.defer_last = None    # newest count held against its capacity
         self.capacity_hint = {}
         self.sizes = {}
         self.zero_imgs = {}
@@ -137,10 +144,15 @@ class GaussianRasterizationSettings(NamedTuple):
 def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier,
                     cov3Ds_precomp, norm3Ds_precomp, extra_attrs, ED, viewmatrix, projmatrix, tanfovx,
                     tanfovy, image_height, image_width, sh, sh_degree, campos, prefiltered, debug,
-                    normalize_norm=False, write_keys=False):
+                    normalize_norm=False, write_keys=False, defer=False):
     """Equivalent of _C.rasterize_gaussians (DGR rasterize_points.cu:35-133).  normalize_norm: the
     kernel also applies the F.normalize(norm, dim=0) of DGR diff_gauss/__init__.py:48.  write_keys:
-    also leave the reference's sorted 64-bit keys in the binning buffer (tests compare them)."""
+    also leave the reference's sorted 64-bit keys in the binning buffer (tests compare them).
+    defer: do not wait for the instance count (the reference's one device->host sync,
+    rasterizer_impl.cu:284): the frame is queued with the instance workspaces of the last frame of
+    this shape that did wait, num_rendered comes back as -1 (pass it on to `_backward_native`), and
+    `check_deferred` later holds the posted count against those workspaces.  The first call of a
+    shape waits whatever `defer` says."""
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     if not means3D.is_cuda:
@@ -192,9 +204,16 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
     geom_ptr = state.data_ptr()
     a.geom, a.img, a.bin, a.sort, a.ctrl = geom_ptr, geom_ptr + geom_bytes, binb.data_ptr(), sort.data_ptr(), ctrl.data_ptr()
     a.capacity = capacity
-    a.num_rendered_pinned = sc.pinned_ptr
+    defer = bool(defer) and sc.capacity_hint.get(hint_key) is not None
+    if defer:
+        if len(sc.defer_pending) >= _DEFER_SLOTS:
+            check_deferred(dev, keep=_DEFER_SLOTS - 1, stream=stream)
+        slot = sc.defer_serial % _DEFER_SLOTS
+        a.num_rendered_pinned = sc.pinned_ptr + 4 * (4 + slot)
+    else:
+        a.num_rendered_pinned = sc.pinned_ptr
     a.ctrl_clean = 1
-    a.defer_count, a.write_keys = 0, int(bool(write_keys))
+    a.defer_count, a.write_keys = int(defer), int(bool(write_keys))
     sc.dirty.add("ctrl")  # until the call has returned without an exception
 
     n = sc.n_out
@@ -209,10 +228,42 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
         if st != N.IGS_OK:
             N.check(st, "forward")
     sc.dirty.discard("ctrl")
+    if defer:
+        sc.defer_pending.append((sc.defer_serial, slot, capacity, hint_key))
+        sc.defer_serial += 1
+        return -1, color, depth, norm, alpha, radii, extra, geom, binb, img
     num_rendered = int(n.value)
     # next call with this shape: 25 % head-room over what this one needed
     sc.capacity_hint[hint_key] = max(int(num_rendered * 1.25) + 4096, 1 << 14)
     return num_rendered, color, depth, norm, alpha, radii, extra, geom, binb, img
+
+
+def check_deferred(device, keep=0, stream=None):
+    """Hold the counts of this (device, stream, thread)'s `defer=True` frames, all but the newest `keep`,
+    against the instance workspaces they were queued with.  Waits for a count that has not been posted
+    yet.  Returns the newest count seen (None if there is none); raises RuntimeError if a frame outgrew
+    its workspaces -- it was not rendered and its backward stood down -- after raising the size the next
+    frame of that shape gets."""
+    device = torch.device(device)
+    if stream is None:
+        stream = torch.cuda.current_stream(device).cuda_stream
+    sc = _get_scratch(device, stream)
+    while len(sc.defer_pending) > keep:
+        serial, slot, capacity, hint_key = sc.defer_pending.pop(0)
+        word = sc.pinned[4 + slot]
+        spins = 0
+        while int(word) == -1:
+            spins += 1
+            if spins % 1024 == 0 and torch.cuda.current_stream(device).query():
+                if int(word) == -1:
+                    raise RuntimeError("libigs_raster: a deferred frame finished without posting its instance count")
+        n = int(word) & 0xFFFFFFFF
+        if n > capacity:
+            sc.capacity_hint[hint_key] = max(int(n * 1.25) + 4096, 1 << 14)
+            raise RuntimeError(f"libigs_raster: deferred frame {serial} has {n} instances, its workspaces hold "
+                               f"{capacity}; it was not rendered (render it again)")
+        sc.defer_last = n
+    return sc.defer_last
 
 
 def gradient_layout(P, M, ED):

@@ -200,3 +200,47 @@ def test_deferred_count_through_the_c_abi():
     finally:
         a.defer_count = 0
         s.dirty.add("ctrl")
+
+
+def test_run_ahead_frames_of_the_python_host_side():
+    """`_forward_native(defer=True)` + `_backward_native(num_rendered=-1)` + `check_deferred`: frames queued
+    without the host reading their count give the images of the waiting calls bit for bit and their
+    gradients to the run-to-run spread of the float atomics;
+    a frame that outgrows its workspaces is not rendered, its backward stands down without touching
+    memory it does not own, and `check_deferred` says so."""
+    from instag_b200 import rasterizer as R
+    sc = U.make_scene(P=3000, W=96, H=80, sh_degree=None, ED=1, scale_mult=2.0, seed=22)
+    t = U.to_torch(sc)
+    g = S.upstream_grads(sc["H"], sc["W"], extra_dims=1, seed=3)
+    tg = {k: torch.from_numpy(v).cuda() for k, v in g.items()}
+    dev = t["means3D"].device
+    w = R._forward_native(*U.raw_args_fwd(t))                       # waits; leaves the capacity hint
+    n0 = int(w[0])
+    want = R._backward_native(*U._bwd_args(t, w[5], tg, w[7], n0, w[8], w[9], w[4]))
+    torch.cuda.synchronize()
+    assert n0 > 0
+    for _ in range(3):                                               # three frames in flight, none read
+        d = R._forward_native(*U.raw_args_fwd(t), defer=True)
+        assert d[0] == -1
+        got = R._backward_native(*U._bwd_args(t, d[5], tg, d[7], -1, d[8], d[9], d[4]))
+    assert R.check_deferred(dev) == n0
+    torch.cuda.synchronize()
+    for a, b in zip(w[1:7], d[1:7]):
+        assert torch.equal(a, b)
+    for a, b in zip(want, got):   # (float atomics: two runs of one frame differ in the last bits)
+        assert a.shape == b.shape and (a.numel() == 0 or U.rel_err(b.cpu().numpy(), a.cpu().numpy()) <= 1e-5)
+    # a hint that is too small for the frame
+    s = R._get_scratch(dev, torch.cuda.current_stream(dev).cuda_stream)
+    key = (3000, sc["H"], sc["W"])
+    assert key in s.capacity_hint
+    s.capacity_hint[key] = n0 // 2
+    d = R._forward_native(*U.raw_args_fwd(t), defer=True)
+    R._backward_native(*U._bwd_args(t, d[5], tg, d[7], -1, d[8], d[9], d[4]))
+    with pytest.raises(RuntimeError, match="not rendered"):
+        R.check_deferred(dev)
+    torch.cuda.synchronize()                                         # nothing faulted
+    assert s.capacity_hint[key] >= n0
+    again = R._forward_native(*U.raw_args_fwd(t), defer=True)
+    R.check_deferred(dev)
+    torch.cuda.synchronize()
+    assert torch.equal(again[1], w[1])

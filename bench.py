@@ -275,10 +275,8 @@ class Arm:
     def num_rendered(self):
         """Instances of the last frame (all deferred counts held against their workspaces first)."""
         if self.run_ahead:
-            n = self.R.check_deferred(self.device, keep=0)
-            if n is not None:
-                return int(n)
-        if self.last and self.last[0] >= 0:
+            self.R.check_deferred(self.device, keep=0)  # (the scratch, and so its last count, is shared by the arms of a process)
+        elif self.last and self.last[0] >= 0:
             return int(self.last[0])
         return int(self.step_fwd_only()[0])
 

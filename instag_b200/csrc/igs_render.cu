@@ -94,10 +94,15 @@ __global__ void __launch_bounds__(RT, IGS_FWD_MIN_CTAS) render_kernel(RenderArgs
   const uint32_t smine = sbase + lane * 16;         // my slot in plane 0; planes are 512 B apart
   const float bg0 = __ldg(a.bg + 0), bg1 = __ldg(a.bg + 1), bg2 = __ldg(a.bg + 2);
 
- for (;;) {
-  int unit = 0;
-  if (lane == 0) unit = (int)atomicAdd(&a.header->render_ticket, 1u);
-  unit = __shfl_sync(0xffffffffu, unit, 0);
+ // the first unit of every warp is its own number (no ticket: all resident warps start at once, and that
+ // many atomics on one word queue up for ~2 us); the tickets hand out the units behind those
+ const int first_wave = (int)gridDim.x * RW;
+ for (bool first = true;; first = false) {
+  int unit = (int)blockIdx.x * RW + warp;
+  if (!first) {
+    if (lane == 0) unit = first_wave + (int)atomicAdd(&a.header->render_ticket, 1u);
+    unit = __shfl_sync(0xffffffffu, unit, 0);
+  }
   if (unit >= num_units) break;
   unsigned long long* const trace = g_trace;
   const unsigned long long t_start = trace ? gtimer() : 0ull;

@@ -147,10 +147,14 @@ __global__ void __launch_bounds__(BT, IGS_BWD_MIN_CTAS) render_backward_kernel(B
   const uint32_t spend = (uint32_t)__cvta_generic_to_shared(&s_pend[warp][0]);
 
  // persistent: every warp pulls (tile, 8x4 block) units from one ticket, heaviest tiles first
- for (;;) {
-  int unit = 0;
-  if (lane == 0) unit = (int)atomicAdd(a.ticket, 1u);
-  unit = __shfl_sync(0xffffffffu, unit, 0);
+ // (the first unit of every warp is its own number, as in the forward)
+ const int first_wave = (int)gridDim.x * BW;
+ for (bool first = true;; first = false) {
+  int unit = (int)blockIdx.x * BW + warp;
+  if (!first) {
+    if (lane == 0) unit = first_wave + (int)atomicAdd(a.ticket, 1u);
+    unit = __shfl_sync(0xffffffffu, unit, 0);
+  }
   if (unit >= num_units) break;
   // consecutive tickets (= the four warps of a CTA, one SM) go to four DIFFERENT tiles, so that
   // an SM's share of the frame is a sum of independent unit costs (groups of 4 tiles x 8 blocks)

@@ -170,7 +170,7 @@ static BinArgs make_bin(const IgsFwdArgs* a) {
   ba.tile_count = (uint32_t*)(c + cl.tile_count);
   ba.tile_cursor = (uint32_t*)(c + cl.tile_cursor);
   ba.ranges = (const uint2*)(im + il.ranges);
-  ba.tile_order = (uint32_t*)(im + il.tile_order);
+  ba.tile_order = (uint4*)(im + il.tile_order);
   ba.scan.num_tiles = ba.num_tiles;
   ba.scan.capacity = a->capacity;
   ba.scan.header = ba.header;
@@ -371,7 +371,7 @@ int igs_backward(const IgsBwdArgs* a, igs_stream_t stream) {
   ra.W = a->W; ra.H = a->H; ra.ED = a->ED;
   ra.grid_x = (a->W + TILE - 1) / TILE; ra.grid_y = (a->H + TILE - 1) / TILE;
   ra.ranges = (const uint2*)(im + il.ranges);
-  ra.tile_order = (const uint32_t*)(im + il.tile_order);
+  ra.tile_order = (const uint4*)(im + il.tile_order);
   ra.point_list = (const uint32_t*)(b + 0); // point_list is the first array of the bin workspace for any capacity
   (void)bl;
   ra.splat = (const float4*)(g + gl.splat);

@@ -107,7 +107,8 @@ __device__ void tile_order(const BinArgs& a) {
   __syncthreads();
   for (int t = t0; t < t1; t++) {
     const uint32_t slot = atomicAdd(&s_bucket[ORDER_BUCKET(TILE_CNT(t))], 1u);
-    a.tile_order[slot] = (uint32_t)t;
+    const uint2 r = __ldcg(a.ranges + t); // (written by this CTA in front of the barriers above, or by the scan kernel)
+    a.tile_order[slot] = make_uint4((uint32_t)t, r.x, r.y, 0u);
   }
 #undef ORDER_BUCKET
 #undef TILE_CNT

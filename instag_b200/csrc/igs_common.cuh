@@ -50,7 +50,7 @@ struct ImgLayout {
     size_t T = (size_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
     size_t o = 0;
     ranges = o;     o = align_up(o + (T ? T : 1) * sizeof(uint2));
-    tile_order = o; o = align_up(o + (T ? T : 1) * sizeof(uint32_t)); // tiles, longest list first
+    tile_order = o; o = align_up(o + (T ? T : 1) * sizeof(uint4));    // {tile, start, end, -}, longest list first
     n_contrib = o;  o = align_up(o + (size_t)(W * H > 0 ? W * H : 1) * sizeof(uint32_t));
     norm_len = o;   o = align_up(o + (size_t)(W * H > 0 ? W * H : 1) * sizeof(float)); // |n| per pixel (fused normalize)
     info = o;       o = align_up(o + 4 * sizeof(uint32_t)); // {num_rendered of this frame, -, -, -}: kept with the state

@@ -44,7 +44,7 @@ struct BinArgs {
   uint32_t* tile_cursor;      // [T*CNT_STRIDE] slots handed out in each tile's segment: relative to the segment start
                               // when the duplicate CTAs scan the counts themselves, else absolute (tile_scan_kernel)
   const uint2* ranges;        // [T] [start, end) of each tile in the sorted list, (0,0) if empty
-  uint32_t* tile_order;       // [T] tile ids, longest list first (the render kernels' unit order)
+  uint4* tile_order;          // [T] {tile id, its range} longest list first: a render unit finds its list with ONE load
   unsigned long long* pairs;  // [capacity] (depth bits << 32 | gaussian id), grouped by tile, unordered inside
   unsigned long long* pairs2; // [capacity] scratch of the two-level sort of segments beyond TS_CAP
   uint32_t* point_list;       // [capacity] sorted
@@ -56,7 +56,7 @@ struct RenderArgs {
   int W, H, ED, grid_x, grid_y;
   CtrlHeader* header; // overflow flag: the tile lists are incomplete, render nothing; unit ticket
   const uint2* ranges;
-  const uint32_t* tile_order;
+  const uint4* tile_order;
   const uint32_t* point_list;
   const float4* splat;
   const float* extra_attrs; // [P,ED], used for channels >= 1
@@ -71,7 +71,7 @@ struct BwdRenderArgs {
   Prof prof;
   int W, H, ED, grid_x, grid_y;
   const uint2* ranges;
-  const uint32_t* tile_order;
+  const uint4* tile_order;
   const uint32_t* point_list;
   const float4* splat;
   const float* extra_attrs;

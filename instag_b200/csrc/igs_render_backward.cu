@@ -161,7 +161,8 @@ __global__ void __launch_bounds__(BT, IGS_BWD_MIN_CTAS) render_backward_kernel(B
   const int num_tiles = a.grid_x * a.grid_y;
   int slot = ((unit >> 5) << 2) + (unit & 3), wb = (unit >> 2) & 7;
   if (((unit >> 5) << 2) + 4 > num_tiles) { slot = unit >> 3; wb = unit & 7; } // ragged last group
-  const int tile = (int)__ldg(a.tile_order + slot);
+  const uint4 entry = __ldg(a.tile_order + slot);
+  const int tile = (int)entry.x;
   const int tx = tile % a.grid_x, ty = tile / a.grid_x;
   const int bx = tx * TILE + (wb & 1) * 8, by = ty * TILE + (wb >> 1) * 4;
   const int px = bx + (lane & 7), py = by + (lane >> 3);
@@ -169,7 +170,7 @@ __global__ void __launch_bounds__(BT, IGS_BWD_MIN_CTAS) render_backward_kernel(B
   const float pxf = (float)px, pyf = (float)py;
   const float wx0 = (float)bx, wx1 = wx0 + 7.f, wy0 = (float)by, wy1 = wy0 + 3.f;
   const size_t pix = (size_t)py * a.W + px;
-  const uint2 range = __ldg(a.ranges + tile);
+  const uint2 range = make_uint2(entry.y, entry.z);
 
   const int last_contributor = inside ? (int)a.n_contrib[pix] : 0;
   // nothing behind the last contributor of any of the warp's pixels matters

@@ -96,14 +96,12 @@ __global__ void __launch_bounds__(RT, IGS_FWD_MIN_CTAS) render_kernel(RenderArgs
 
  // the first unit of every warp is its own number (no ticket: all resident warps start at once, and that
  // many atomics on one word queue up for ~2 us); the tickets hand out the units behind those
- const int first_wave = (int)gridDim.x * RW;
- for (bool first = true;; first = false) {
-  int unit = (int)blockIdx.x * RW + warp;
-  if (!first) {
-    if (lane == 0) unit = first_wave + (int)atomicAdd(&a.header->render_ticket, 1u);
-    unit = __shfl_sync(0xffffffffu, unit, 0);
-  }
-  if (unit >= num_units) break;
+ auto next_unit = [&]() {
+   int u = 0;
+   if (lane == 0) u = (int)gridDim.x * RW + (int)atomicAdd(&a.header->render_ticket, 1u);
+   return __shfl_sync(0xffffffffu, u, 0);
+ };
+ for (int unit = (int)blockIdx.x * RW + warp; unit < num_units; unit = next_unit()) {
   unsigned long long* const trace = g_trace;
   const unsigned long long t_start = trace ? gtimer() : 0ull;
   // consecutive tickets (= the four warps of a CTA, one SM) go to four DIFFERENT tiles, so that
@@ -160,10 +158,15 @@ __global__ void __launch_bounds__(RT, IGS_FWD_MIN_CTAS) render_kernel(RenderArgs
     unsigned m = __ballot_sync(0xffffffffu, hit);
     if (trace) { tr_chunks++; tr_surv += __popc(m); }
     const uint32_t id_mine = id_cur;
-    const float4 c0 = q0, c1 = q1;
     // this chunk's r2 / r3 planes have landed; everybody is done reading the previous chunk's slots
     copies_wait();
     __syncwarp();
+    // survivors park the half of their record the cull used, from the registers the prefetch below reuses
+    if (hit) {
+      sts128(smine, q0);
+      sts128(smine + 512, q1);
+      if (ED_T < 0) s_id[warp][lane] = id_mine;
+    }
     // prefetch the next chunk's cull data and colour / normal planes, and the ids of the chunk after it
     id_cur = id_nxt;
     const uint32_t cur = sbase + 1024 + par * 1024; // r2 plane of this chunk (r3: +512)
@@ -178,11 +181,6 @@ __global__ void __launch_bounds__(RT, IGS_FWD_MIN_CTAS) render_kernel(RenderArgs
     copies_commit();
     if (cb + 64 + lane < total) id_nxt = __ldg(list + cb + 64 + lane);
     if (m == 0) continue;
-    if (hit) {
-      sts128(smine, c0);
-      sts128(smine + 512, c1);
-      if (ED_T < 0) s_id[warp][lane] = id_mine;
-    }
     __syncwarp();
     // G survivors per trip.  Their alpha chains are independent (instruction-level parallelism for a
     // warp that is alone on its scheduler at the end of the frame); only the transmittance recurrence is

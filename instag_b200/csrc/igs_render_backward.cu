@@ -67,6 +67,10 @@ __device__ __forceinline__ void sts128b(uint32_t addr, float4 v) {
 __device__ __forceinline__ void copy4_async(uint32_t dst, const void* src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
 }
+__device__ __forceinline__ void copy16_async_b(uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void copies_wait_planes_b() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 __device__ __forceinline__ void copies_commit_b() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void copies_wait_b() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ float rcp_approx(float x) {
@@ -86,22 +90,33 @@ struct PixelBack {
 
 template <int ED_T> // 0, 1, or -1 = generic
 __global__ void __launch_bounds__(BT, IGS_BWD_MIN_CTAS) render_backward_kernel(BwdRenderArgs a) {
-  __shared__ float4 s_rec[BW][4][32];
-  __shared__ uint32_t s_id[BW][32];
-  // ids of the chunk after next, copied in asynchronously (double buffered).  In a register the prefetched
-  // id was spilled to local memory at 80 registers, and the spill store waited for the load it had just
-  // issued: 5 % of the kernel's stall samples sat on that one instruction.
-  __shared__ uint32_t s_idn[BW][2][32];
-  // parked blend weights [0] and g = G*dL/dalpha [1] of up to PEND splats; pixel p of slot s sits
-  // in column p ^ ((s & 1) << 4) so that both the scalar stores and the 16-byte fragment loads are
-  // bank-conflict free
-  __shared__ __align__(128) float s_wg[BW][2][PEND][32]; // (the swizzle works on address bits: keep 128-byte alignment)
+  // Everything a warp owns sits in ONE block, so that one base register and immediate offsets address it
+  // all (separate arrays cost a base register each, and the kernel lives at the 80-register line):
+  //   rec  [4][32] float4  the staged records of the chunk's survivors, one 512-byte plane per 16 bytes
+  //   wg   [2][PEND][32]   parked blend weights [0] and g = G*dL/dalpha [1] of up to PEND splats; pixel p of
+  //                        slot s sits in column p ^ ((s & 1) << 4) so that both the scalar stores and the
+  //                        16-byte fragment loads are bank-conflict free (the swizzle works on address
+  //                        bits: the block is 128-byte aligned and wg starts at a multiple of 128)
+  //   bf   [4][32] float4  right-hand fragments, one float4 per lane: [0..1] dL_dpixel TF32 hi, [2..3] lo
+  //   id   [32]            Gaussian ids of the staged records
+  struct __align__(128) WarpBlock {
+    float4 rec[4][32];
+    float wg[2][PEND][32];
+    float4 bf[4][32];
+    uint32_t id[32];
+  };
+  constexpr uint32_t WB_WG = 2048, WB_BF = 6144, WB_ID = 8192;
+  static_assert(sizeof(WarpBlock) == 8320 && sizeof(WarpBlock) % 128 == 0, "offsets below");
+  __shared__ WarpBlock s_w[BW];
+  // ids of the chunk after next, copied in asynchronously (double buffered; the buffers of a warp are
+  // told apart by address bit 7).  In a register the prefetched id was spilled to local memory at 80
+  // registers, and the spill store waited for the load it had just issued: 5 % of the kernel's stall
+  // samples sat on that one instruction.
+  __shared__ __align__(256) uint32_t s_idn[BW][2][32];
   // 512-byte stride per warp (PEND = 16 records used): the fill level of a warp's queue is then
   // (address & 511) >> 4, with no base address to keep in (or recompute into) a register
   __shared__ __align__(512) float4 s_pend[BW][32]; // {mean.x, mean.y, gaussian id bits, -}
-  // right-hand fragments, one float4 per lane: [0..1] dL_dpixel TF32 hi, [2..3] lo (per unit),
-  // and the moment basis (the same for every warp and unit)
-  __shared__ float4 s_bf[BW][4][32];
+  // the moment basis (the same for every warp and unit)
   __shared__ float4 s_bm[2][32];
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -117,15 +132,15 @@ __global__ void __launch_bounds__(BT, IGS_BWD_MIN_CTAS) render_backward_kernel(B
   const int num_units = a.grid_x * a.grid_y * 8;
   const int ED = ED_T < 0 ? a.ED : ED_T;
   const size_t HW = (size_t)a.H * a.W;
-  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(&s_rec[warp][0][0]);
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(&s_w[warp]);
   const uint32_t smine = sbase + lane * 16;
-  const uint32_t sidb = (uint32_t)__cvta_generic_to_shared(&s_id[warp][0]);
+  const uint32_t sidb = sbase + WB_ID;
   const uint32_t sidn = (uint32_t)__cvta_generic_to_shared(&s_idn[warp][0][lane]); // + 128: the other buffer
   const float bg0 = __ldg(a.bg), bg1 = __ldg(a.bg + 1), bg2 = __ldg(a.bg + 2);
   // mma fragment coordinates: this lane owns rows fg, fg+8 (splat slots) of A and C, and the
   // k-columns ft, ft+4; k-step 2q+h of the product covers pixels 16q + 4*ft + {2h, 2h+1}
   const int fg = lane >> 2, ft = lane & 3;
-  const uint32_t swg = (uint32_t)__cvta_generic_to_shared(&s_wg[warp][0][0][0]);
+  const uint32_t swg = sbase + WB_WG;
   const uint32_t sfrag = swg + fg * 128 + ft * 16; // + (q ^ (fg & 1)) * 64: the slot's swizzle (+8 slots: +1024, g: +2048)
   // moment basis of the pixels of this lane's k-columns, row fg of the right-hand matrix:
   // {1, lx, lx^2, lx*ly, ly^2, ly, 0, 0}; small integers, exact in TF32
@@ -142,20 +157,18 @@ __global__ void __launch_bounds__(BT, IGS_BWD_MIN_CTAS) render_backward_kernel(B
     }
   }
   __syncthreads();
-  const uint32_t sbf = (uint32_t)__cvta_generic_to_shared(&s_bf[warp][0][lane]);
+  const uint32_t sbf = smine + WB_BF;
   const uint32_t sbm = (uint32_t)__cvta_generic_to_shared(&s_bm[0][lane]);
   const uint32_t spend = (uint32_t)__cvta_generic_to_shared(&s_pend[warp][0]);
 
  // persistent: every warp pulls (tile, 8x4 block) units from one ticket, heaviest tiles first
  // (the first unit of every warp is its own number, as in the forward)
- const int first_wave = (int)gridDim.x * BW;
- for (bool first = true;; first = false) {
-  int unit = (int)blockIdx.x * BW + warp;
-  if (!first) {
-    if (lane == 0) unit = first_wave + (int)atomicAdd(a.ticket, 1u);
-    unit = __shfl_sync(0xffffffffu, unit, 0);
-  }
-  if (unit >= num_units) break;
+ auto next_unit = [&]() {
+   int u = 0;
+   if (lane == 0) u = (int)gridDim.x * BW + (int)atomicAdd(a.ticket, 1u);
+   return __shfl_sync(0xffffffffu, u, 0);
+ };
+ for (int unit = (int)blockIdx.x * BW + warp; unit < num_units; unit = next_unit()) {
   // consecutive tickets (= the four warps of a CTA, one SM) go to four DIFFERENT tiles, so that
   // an SM's share of the frame is a sum of independent unit costs (groups of 4 tiles x 8 blocks)
   const int num_tiles = a.grid_x * a.grid_y;
@@ -200,7 +213,7 @@ __global__ void __launch_bounds__(BT, IGS_BWD_MIN_CTAS) render_backward_kernel(B
   // right-hand matrix of the attribute product: dL_dpixel channel fg at this lane's k-columns,
   // transposed through shared memory once per unit and split into TF32 hi + lo
   {
-    float* sD = &s_wg[warp][0][0][0];
+    float* sD = &s_w[warp].wg[0][0][0];
     sD[lane] = dpc0; sD[32 + lane] = dpc1; sD[64 + lane] = dpc2; sD[96 + lane] = dpd;
     sD[128 + lane] = dpn0; sD[160 + lane] = dpn1; sD[192 + lane] = dpn2; sD[224 + lane] = dpe0;
     __syncwarp();
@@ -352,8 +365,19 @@ __global__ void __launch_bounds__(BT, IGS_BWD_MIN_CTAS) render_backward_kernel(B
                                              wx0, wx1, wy0, wy1);
     unsigned m = __ballot_sync(0xffffffffu, hit);
     const uint32_t id_mine = id_cur;
-    const float4 c0 = q0, c1 = q1;
     copies_wait_b(); // the next chunk's ids (issued one chunk ago; a lane reads the word it copied itself)
+    // Survivors stage their record: the half the cull used goes from its registers (which the prefetch
+    // below then reuses), the colour / normal half is copied global -> shared without a register.  Nobody
+    // still reads the slots: the ballot above is behind every lane's last trip of the previous chunk.
+    if (hit) {
+      const float4* rec = a.splat + (size_t)id_mine * SPLAT_F4;
+      sts128b(smine, q0);
+      sts128b(smine + 512, q1);
+      copy16_async_b(smine + 1024, rec + 2);
+      copy16_async_b(smine + 1536, rec + 3);
+      asm volatile("st.shared.u32 [%0], %1;" ::"r"(sidb + lane * 4), "r"(id_mine) : "memory");
+    }
+    copies_commit_b(); // group 1 of the chunk: the planes
     if (cb + 32 + lane < wmax) {
       asm volatile("ld.shared.u32 %0, [%1];" : "=r"(id_cur) : "r"(nbuf));
       q0 = __ldg(a.splat + (size_t)id_cur * SPLAT_F4);
@@ -361,18 +385,9 @@ __global__ void __launch_bounds__(BT, IGS_BWD_MIN_CTAS) render_backward_kernel(B
     }
     nbuf ^= 128u;
     if (cb + 64 + lane < wmax) copy4_async(nbuf, list + (wmax - 65 - cb - lane));
-    copies_commit_b();
+    copies_commit_b(); // group 2: the ids of the chunk after next
     if (m == 0) continue;
-    __syncwarp();
-    if (hit) {
-      const float4* rec = a.splat + (size_t)id_mine * SPLAT_F4;
-      const float4 c2 = __ldg(rec + 2), c3 = __ldg(rec + 3);
-      sts128b(smine, c0);
-      sts128b(smine + 512, c1);
-      sts128b(smine + 1024, c2);
-      sts128b(smine + 1536, c3);
-      s_id[warp][lane] = id_mine;
-    }
+    copies_wait_planes_b(); // all but the newest group: the planes are in, the ids may still travel
     __syncwarp();
     const int jmin = wmax - 1 - cb - last_contributor; // entry j is in front of this pixel's last contributor iff j > jmin
     // two staged splats per trip: the two alpha evaluations are independent, the recurrences run in order

@@ -13,6 +13,7 @@ echo "# SASS evidence ($(basename $LIB), sm_100a, $(date -u +%F)); register numb
 show "render_backward_kernelILi1" "HMMA" "render_backward_kernel<1>: pixel sums on the tensor cores (mma.sync m16n8k8 TF32, hi/lo split)"
 show "render_backward_kernelILi1" "REDG" "render_backward_kernel<1>: 8-byte vector reductions into the accumulator rows (red.global.add.v2.f32)"
 show "render_backward_kernelILi1" "MUFU" "render_backward_kernel<1>: exp / reciprocal"
+show "render_backward_kernelILi1" "LDGSTS|LDGDEPBAR|DEPBAR" "render_backward_kernel<1>: list ids (4 bytes) and the survivors' colour / normal planes (16 bytes) by cp.async; wait_group 1 = all but the ids"
 show "render_kernelILi1" "LDGSTS|LDGDEPBAR|DEPBAR" "render_kernel<1>: colour / normal planes by cp.async (LDGSTS) one chunk ahead"
 show "render_kernelILi1" "ACQBULK|PREEXIT|ATOMG" "render_kernel<1>: griddepcontrol.wait (ACQBULK), unit ticket (ATOMG)"
 show "preprocess_kernelILb0ELb1" "ACQBULK|ATOMS|REDG|DFMA" "preprocess_kernel<precomp, smem histogram>: dependent launch, shared-memory tile histogram (ATOMS), flush (REDG), ndc2Pix in double (DFMA)"

@@ -10,6 +10,8 @@ functions (which call `diff_gauss`, i.e. this library); what changes is everythi
 * `FrameRing` -- the uint8 frame is written into a device ring slot and copied to pinned host
   memory on a side stream; the reference blocks on `.cpu().numpy()` every frame
   (synthesize_fuse.py:76), which serialises rendering and the PCIe copy;
+* `RecordedFrames` -- the device work of a frame recorded once into CUDA graphs and replayed, for
+  callers whose per-frame inputs live in buffers of fixed address;
 * `synthesize_sequence` -- the frames of a sequence are independent (read-only models, one
   camera/audio window per frame), so rank r of world renders frames r, r+world, ...; there is
   no collective on the render path.
@@ -184,6 +186,55 @@ class DeferredCounts:
         finally:
             if self.b is not None:
                 self.b.set_deferred_counts(was)
+
+
+class RecordedFrames:
+    """The device work of one synthesis frame recorded ONCE per ring slot into CUDA graphs and replayed.
+
+    Nothing in a frame of this library depends on the host (the instance counts are posted, not
+    fetched), so a frame -- both rasterizations, the compose kernel into the ring slot -- can be recorded
+    through the module API and replayed with one call per frame.  `frame_fn(out)` queues the frame's
+    kernels on the current stream and composes into the uint8 [H,W,3] tensor `out`; everything that
+    changes from frame to frame (cameras, deformed Gaussians) must reach it through buffers whose
+    ADDRESSES stay the same: the caller copies the frame's inputs into them, then calls `render(tag)`.
+    The reference cannot be driven this way (its forward sizes buffers on the host from a count it reads
+    back in the middle, rasterizer_impl.cu:284).
+
+    The recorded workspaces are those of the warm-up frames with the library's head-room (2x the largest
+    instance count seen); `overflowed()` tells after the fact whether a replayed frame outgrew them -- its
+    kernels then stood down and the frame is not valid."""
+
+    def __init__(self, frame_fn, ring, warmup=3):
+        from . import rasterizer as R
+        if R.host_path() != "cxx":
+            raise RuntimeError("RecordedFrames needs the compiled host side (IGS_HOST=python does not record)")
+        self.ring, self.binding = ring, R.binding()
+        dev = ring.device
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        self.graphs, pool = [], None
+        with torch.no_grad(), torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):  # workspaces, capacity hints, streams of the frame function
+                frame_fn(ring.dev[0])
+            side.synchronize()
+            for i in range(ring.depth):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=side, pool=pool):
+                    frame_fn(ring.dev[i])
+                pool = g.pool() if pool is None else pool
+                self.graphs.append(g)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+
+    def render(self, tag=None):
+        """Replay the frame into the ring's next slot (current stream) and queue its device->host copy."""
+        if self.ring.full():
+            raise RuntimeError("FrameRing is full: collect() before rendering another frame")
+        self.graphs[self.ring.head % self.ring.depth].replay()
+        self.ring.commit(tag)
+
+    def overflowed(self):
+        return bool(self.binding.captured_overflowed())
 
 
 def synthesize_sequence(views, render_face, render_mouth, dilate=False, rank=0, world=1, ring_depth=8,

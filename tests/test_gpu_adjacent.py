@@ -396,3 +396,69 @@ def test_deferred_counts_give_the_same_frames_and_repair_a_frame_that_was_cut_sh
     with torch.no_grad():
         face(views[0])
     assert b.deferred_mark() == s1
+
+
+def test_recorded_frames_equal_the_eager_frames():
+    """synthesis.RecordedFrames: a frame (face pass, mouth pass on a side stream, compose into the ring slot)
+    recorded once per slot into CUDA graphs and replayed with the camera refreshed in place gives, frame for
+    frame, the bytes of the eager loop."""
+    import torch
+    from diff_gauss import GaussianRasterizer
+    from instag_b200 import rasterizer as R
+    from instag_b200 import synthesis as SY
+    from instag_b200 import synthetic as S
+    if R.host_path() != "cxx":
+        pytest.skip("the compiled host side records; IGS_HOST=python does not")
+    H = W = 128
+    dev = torch.device("cuda", torch.cuda.current_device())
+    clouds = [U.to_torch(S.make_cloud(4000, sh_degree=1, M=4, seed=0, scale_mult=2.0), dev),
+              U.to_torch(S.make_cloud(1500, sh_degree=1, M=4, seed=1, scale_mult=2.0), dev)]
+    cams = S.camera_sequence(7, W, H, seed=5)
+    # one block of fixed address for what changes per frame: view matrix | projection matrix | camera position
+    block = torch.zeros(36, dtype=torch.float32, device=dev)
+    packed = [torch.from_numpy(np.concatenate([c["viewmatrix"].reshape(-1), c["projmatrix"].reshape(-1),
+                                               c["campos"].reshape(-1), np.zeros(1, np.float32)]).astype(np.float32)).to(dev)
+              for c in cams]
+    tsc = dict(U.to_torch(dict(cams[0], bg=np.zeros(3, np.float32)), dev))
+    tsc.update(viewmatrix=block[0:16], projmatrix=block[16:32], campos=block[32:35])
+    settings = [U.settings_from({**cl, **tsc}) for cl in clouds]
+    m2 = [torch.zeros_like(cl["means3D"]) for cl in clouds]
+    bgimg = torch.full((3, H, W), 127.0, device=dev)
+    pair = SY.PairOverlap(dev)
+
+    def render(k):
+        cl = clouds[k]
+
+        def fn(_view):
+            o = GaussianRasterizer(settings[k])(means3D=cl["means3D"], means2D=m2[k], shs=cl["shs"], opacities=cl["opacities"],
+                                                scales=cl["scales"], rotations=cl["rotations"], extra_attrs=cl.get("extra_attrs"))
+            return {"render": o[0], "alpha": o[3]}
+        return fn
+    render_face, render_mouth = render(0), render(1)
+
+    def frame(out):
+        face, mouth = pair(render_face, render_mouth, None)
+        SY.compose_frame(face["render"], face["alpha"], mouth["render"], mouth["alpha"], bgimg, dilate=True, out=out)
+
+    want = []
+    with torch.no_grad():
+        for p in packed:
+            block.copy_(p)
+            out = torch.empty((H, W, 3), dtype=torch.uint8, device=dev)
+            frame(out)
+            want.append(out.cpu().numpy())
+    ring = SY.FrameRing(H, W, depth=3, device=dev)
+    block.copy_(packed[0])
+    rec = SY.RecordedFrames(frame, ring)
+    got = {}
+    for i, p in enumerate(packed):
+        if ring.full():
+            got.update(dict(ring.collect(block=True)))
+        block.copy_(p, non_blocking=True)
+        rec.render(i)
+    got.update(dict(ring.collect(block=True)))
+    assert not rec.overflowed()
+    assert sorted(got) == list(range(len(packed)))
+    assert int((want[0] != 127).sum()) > 1000 and not np.array_equal(want[0], want[3])
+    for i in range(len(packed)):
+        assert np.array_equal(got[i], want[i]), i
